@@ -1,0 +1,317 @@
+"""ctypes binding of ``include/b200_imagenet.h`` (the C ABI of the sm_100a kernels).
+
+There is no CPU fallback: if the shared library is missing or a call returns a non-zero code this
+module raises.  The thin wrappers below take torch CUDA tensors only for their device pointers,
+sizes and the current stream; all arithmetic happens in the CUDA kernels.
+"""
+import ctypes
+import os
+import threading
+
+import torch
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libb200_imagenet.so")
+
+F32, BF16 = 0, 1
+ACT_NONE, ACT_RELU, ACT_ADD_RELU = 0, 1, 2
+LAYOUT_NHWC, LAYOUT_NCHW = 0, 1
+ABI_VERSION = 1
+
+_c = ctypes
+_vp, _i64, _i32, _f32, _sz = _c.c_void_p, _c.c_int64, _c.c_int, _c.c_float, _c.c_size_t
+
+# name -> (restype, argtypes); mirrors include/b200_imagenet.h one to one
+SIGNATURES = {
+    "b200_abi_version": (_i32, []),
+    "b200_error_string": (_c.c_char_p, [_i32]),
+    "b200_tune_set": (_i32, [_c.c_char_p, _i32]),
+    "b200_sgd_flat_f32": (_i32, [_vp, _vp, _vp, _vp, _i64, _f32, _f32, _f32, _f32, _i32, _vp]),
+    "b200_ce_topk_workspace_bytes": (_sz, [_i64]),
+    "b200_ce_topk_fwd": (_i32, [_vp, _vp, _vp, _vp, _vp, _sz, _i64, _i64, _i32, _vp]),
+    "b200_ce_bwd": (_i32, [_vp, _vp, _vp, _vp, _f32, _vp, _i64, _i64, _i32, _vp]),
+    "b200_bn_vec": (_i32, [_i32]),
+    "b200_bn_workspace_bytes": (_sz, [_i64, _i32, _i32]),
+    "b200_bn_fwd_train": (_i32, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _sz, _i64, _i32, _f32, _f32,
+                                 _i32, _i32, _vp]),
+    "b200_bn_fwd_eval": (_i32, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _i64, _i32, _f32, _i32, _i32, _vp]),
+    "b200_bn_bwd": (_i32, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _sz, _i64, _i32, _i32, _i32, _vp]),
+    "b200_input_workspace_bytes": (_sz, [_i64, _i32, _i32, _i32, _i32]),
+    "b200_input_crop_resize_flip_norm": (_i32, [_vp, _vp, _vp, _vp, _vp, _sz, _i64, _i32, _i32, _i32, _i32,
+                                                _c.POINTER(_f32), _c.POINTER(_f32), _i32, _i32, _vp]),
+}
+
+_lib = None
+_lock = threading.Lock()
+
+
+class B200Error(RuntimeError):
+    pass
+
+
+def load():
+    """dlopen the library (once).  Raises B200Error when it has not been built - no fallback."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    with _lock:
+        if _lib is not None:
+            return _lib
+        if not os.path.exists(LIB_PATH):
+            raise B200Error(
+                f"{LIB_PATH} is missing: build it with `python -m imagent_distributed_training_pytorch_with_slurm_b200.build` "
+                "(nvcc, sm_100a). There is no CPU or PyTorch fallback for these kernels.")
+        lib = ctypes.CDLL(LIB_PATH)
+        for name, (res, args) in SIGNATURES.items():
+            fn = getattr(lib, name)  # AttributeError = header/library mismatch
+            fn.restype = res
+            fn.argtypes = args
+        v = lib.b200_abi_version()
+        if v != ABI_VERSION:
+            raise B200Error(f"ABI version mismatch: library {v}, binding {ABI_VERSION}")
+        _lib = lib
+    return _lib
+
+
+def _check(code, what):
+    if code != 0:
+        msg = load().b200_error_string(code)
+        raise B200Error(f"{what} failed: {msg.decode() if msg else code} (code {code})")
+
+
+def tune_set(key, value):
+    _check(load().b200_tune_set(key.encode(), int(value)), f"b200_tune_set({key})")
+
+
+def dtype_code(t):
+    if t.dtype == torch.float32:
+        return F32
+    if t.dtype == torch.bfloat16:
+        return BF16
+    raise B200Error(f"unsupported activation dtype {t.dtype}")
+
+
+def _ptr(t):
+    return None if t is None else t.data_ptr()
+
+
+def _stream():
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _need_cuda(*ts):
+    for t in ts:
+        if t is not None and not t.is_cuda:
+            raise B200Error("B200 kernels need CUDA tensors; there is no CPU path")
+
+
+# ---- launch accounting / per-kernel timing -----------------------------------------------------
+class _Stats:
+    """Counts our kernel launches and, when enabled, brackets chosen entry points with CUDA events
+    on the launching stream so bench.py can report achieved GB/s of one kernel family."""
+
+    def __init__(self):
+        self.launches = 0
+        self.timed = None  # set of family names or None
+        self.records = []  # (family, bytes, start_event, end_event)
+
+    def reset(self):
+        self.launches = 0
+        self.records = []
+
+    def begin(self, family):
+        if self.timed is not None and family in self.timed:
+            e = torch.cuda.Event(enable_timing=True)
+            e.record()
+            return e
+        return None
+
+    def end(self, family, n_launch, start, nbytes):
+        self.launches += n_launch
+        if start is not None:
+            e = torch.cuda.Event(enable_timing=True)
+            e.record()
+            self.records.append((family, nbytes, start, e))
+
+    def summary(self):
+        out = {}
+        for fam, nbytes, s, e in self.records:
+            d = out.setdefault(fam, {"calls": 0, "bytes": 0, "ms": 0.0})
+            d["calls"] += 1
+            d["bytes"] += nbytes
+            d["ms"] += s.elapsed_time(e)
+        return out
+
+
+stats = _Stats()
+
+_workspaces = {}
+
+
+def workspace(dev, nbytes, tag, zero=False):
+    """Cached per-(device, tag) scratch buffer, grown on demand (PyTorch's allocator owns it)."""
+    key = (dev.index if dev.index is not None else torch.cuda.current_device(), tag)
+    buf = _workspaces.get(key)
+    if buf is None or buf.numel() < nbytes:
+        n = max(int(nbytes), 256)
+        buf = torch.zeros(n, dtype=torch.uint8, device=dev) if zero else torch.empty(n, dtype=torch.uint8, device=dev)
+        _workspaces[key] = buf
+    return buf
+
+
+# ---- K4b ------------------------------------------------------------------------------------------
+def sgd_flat(p, g, buf, shadow, lr, weight_decay, momentum, grad_scale, first_step):
+    _need_cuda(p, g, buf, shadow)
+    n = p.numel()
+    assert p.dtype == g.dtype == buf.dtype == torch.float32 and g.numel() == n and buf.numel() == n
+    assert p.is_contiguous() and g.is_contiguous() and buf.is_contiguous()
+    if shadow is not None:
+        assert shadow.dtype == torch.bfloat16 and shadow.numel() == n and shadow.is_contiguous()
+    s = stats.begin("sgd")
+    _check(load().b200_sgd_flat_f32(_ptr(p), _ptr(g), _ptr(buf), _ptr(shadow), n, lr, weight_decay, momentum,
+                                    grad_scale, 1 if first_step else 0, _stream()), "b200_sgd_flat_f32")
+    stats.end("sgd", 1, s, n * ((16 if first_step else 20) + (2 if shadow is not None else 0)))
+
+
+# ---- K3 -------------------------------------------------------------------------------------------
+def ce_topk_fwd(logits, target, out3=None):
+    """Returns (out3 float32[3] = loss, top1 %, top5 %; row_lse float32[N])."""
+    _need_cuda(logits, target)
+    assert logits.dim() == 2 and logits.is_contiguous() and target.dtype == torch.int64 and target.is_contiguous()
+    n, c = logits.shape
+    assert target.numel() == n
+    lib = load()
+    if out3 is None:
+        out3 = torch.empty(3, dtype=torch.float32, device=logits.device)
+    assert out3.dtype == torch.float32 and out3.numel() == 3 and out3.is_contiguous()
+    row_lse = torch.empty(n, dtype=torch.float32, device=logits.device)
+    nbytes = lib.b200_ce_topk_workspace_bytes(n)
+    ws = workspace(logits.device, nbytes, "ce", zero=True)
+    s = stats.begin("ce_topk_fwd")
+    _check(lib.b200_ce_topk_fwd(_ptr(logits), _ptr(target), _ptr(out3), _ptr(row_lse), _ptr(ws), ws.numel(), n, c,
+                                dtype_code(logits), _stream()), "b200_ce_topk_fwd")
+    stats.end("ce_topk_fwd", 1, s, n * c * logits.element_size() + 8 * n + 12)
+    return out3, row_lse
+
+
+def ce_bwd(logits, target, row_lse, grad_out=None, scale=1.0):
+    _need_cuda(logits, target, row_lse, grad_out)
+    n, c = logits.shape
+    dlogits = torch.empty_like(logits)
+    if grad_out is not None:
+        assert grad_out.dtype == torch.float32 and grad_out.numel() == 1
+    s = stats.begin("ce_bwd")
+    _check(load().b200_ce_bwd(_ptr(logits), _ptr(target), _ptr(row_lse), _ptr(grad_out), scale, _ptr(dlogits), n, c,
+                              dtype_code(logits), _stream()), "b200_ce_bwd")
+    stats.end("ce_bwd", 1, s, 2 * n * c * logits.element_size() + 12 * n)
+    return dlogits
+
+
+# ---- K2 -------------------------------------------------------------------------------------------
+def _rows_channels(x):
+    """(M, C) of a channels-last 4-d tensor or a contiguous 2-d [M, C] tensor."""
+    if x.dim() == 4:
+        if not x.is_contiguous(memory_format=torch.channels_last):
+            raise B200Error("BatchNorm kernels need channels-last (NHWC) activations")
+        n, c, h, w = x.shape
+        return n * h * w, c
+    if x.dim() == 2 and x.is_contiguous():
+        return x.shape[0], x.shape[1]
+    raise B200Error("expected a channels-last 4-d or contiguous 2-d activation")
+
+
+def bn_vec(dtype):
+    return load().b200_bn_vec(F32 if dtype == torch.float32 else BF16)
+
+
+def bn_fwd_train(x, z, gamma, beta, running_mean, running_var, num_batches_tracked, eps, momentum, act):
+    """Returns (y, saved float32[4,C], mask uint8 or None)."""
+    _need_cuda(x, z, gamma, beta)
+    m, c = _rows_channels(x)
+    lib = load()
+    dt = dtype_code(x)
+    y = torch.empty_like(x)
+    saved = torch.empty(4, c, dtype=torch.float32, device=x.device)
+    mask = None
+    if act == ACT_ADD_RELU:
+        assert z is not None and z.shape == x.shape and z.dtype == x.dtype
+        _rows_channels(z)
+        mask = torch.empty(m * (c // lib.b200_bn_vec(dt)), dtype=torch.uint8, device=x.device)
+    nbytes = lib.b200_bn_workspace_bytes(m, c, dt)
+    ws = workspace(x.device, nbytes, "bn")
+    s = stats.begin("bn_fwd")
+    _check(lib.b200_bn_fwd_train(_ptr(x), _ptr(z), _ptr(y), _ptr(mask), _ptr(gamma), _ptr(beta), _ptr(running_mean),
+                                 _ptr(running_var), _ptr(num_batches_tracked), _ptr(saved), _ptr(ws), ws.numel(), m, c,
+                                 eps, momentum, act, dt, _stream()), "b200_bn_fwd_train")
+    e = m * c * x.element_size()
+    stats.end("bn_fwd", 3, s, (4 if act == ACT_ADD_RELU else 3) * e + (mask.numel() if mask is not None else 0))
+    return y, saved, mask
+
+
+def bn_fwd_eval(x, z, gamma, beta, running_mean, running_var, eps, act):
+    _need_cuda(x, z, gamma, beta, running_mean, running_var)
+    m, c = _rows_channels(x)
+    y = torch.empty_like(x)
+    s = stats.begin("bn_eval")
+    _check(load().b200_bn_fwd_eval(_ptr(x), _ptr(z), _ptr(y), _ptr(gamma), _ptr(beta), _ptr(running_mean),
+                                   _ptr(running_var), m, c, eps, act, dtype_code(x), _stream()), "b200_bn_fwd_eval")
+    stats.end("bn_eval", 1, s, (3 if act == ACT_ADD_RELU else 2) * m * c * x.element_size())
+    return y
+
+
+def bn_bwd(dy, x, mask, gamma, saved, act, dgamma=None, dbeta=None):
+    """Returns (dx, dz or None, dgamma, dbeta); dgamma/dbeta may be preallocated float32 views
+    (e.g. slices of the flat gradient buffer) and are overwritten."""
+    _need_cuda(dy, x, gamma, saved)
+    m, c = _rows_channels(x)
+    if dy.shape != x.shape or dy.dtype != x.dtype:
+        raise B200Error("dy must match x")
+    _rows_channels(dy)
+    lib = load()
+    dt = dtype_code(x)
+    dx = torch.empty_like(x)
+    dz = torch.empty_like(x) if act == ACT_ADD_RELU else None
+    if dgamma is None:
+        dgamma = torch.empty(c, dtype=torch.float32, device=x.device)
+    if dbeta is None:
+        dbeta = torch.empty(c, dtype=torch.float32, device=x.device)
+    nbytes = lib.b200_bn_workspace_bytes(m, c, dt)
+    ws = workspace(x.device, nbytes, "bn")
+    s = stats.begin("bn_bwd")
+    _check(lib.b200_bn_bwd(_ptr(dy), _ptr(x), _ptr(mask), _ptr(gamma), _ptr(saved), _ptr(dx), _ptr(dz), _ptr(dgamma),
+                           _ptr(dbeta), _ptr(ws), ws.numel(), m, c, act, dt, _stream()), "b200_bn_bwd")
+    e = m * c * x.element_size()
+    stats.end("bn_bwd", 3, s, (6 if act == ACT_ADD_RELU else 5) * e + (2 * mask.numel() if mask is not None else 0))
+    return dx, dz, dgamma, dbeta
+
+
+# ---- K1 -------------------------------------------------------------------------------------------
+def input_stage(images, boxes, flips, out_h, out_w, mean, std, out_dtype=torch.bfloat16, layout=LAYOUT_NHWC):
+    """images uint8 [N,Hs,Ws,3] (device), boxes int32 [N,4] (device), flips uint8 [N] (device) or
+    None.  Returns [N,3,out_h,out_w] logical NCHW: channels-last strides for LAYOUT_NHWC,
+    contiguous for LAYOUT_NCHW."""
+    _need_cuda(images, boxes, flips)
+    assert images.dtype == torch.uint8 and images.dim() == 4 and images.shape[3] == 3 and images.is_contiguous()
+    assert boxes.dtype == torch.int32 and boxes.is_contiguous() and boxes.shape == (images.shape[0], 4)
+    if flips is not None:
+        assert flips.dtype == torch.uint8 and flips.is_contiguous() and flips.numel() == images.shape[0]
+    n, sh, sw, _ = images.shape
+    lib = load()
+    if layout == LAYOUT_NHWC:
+        out = torch.empty((n, 3, out_h, out_w), dtype=out_dtype, device=images.device,
+                          memory_format=torch.channels_last)
+    else:
+        out = torch.empty((n, 3, out_h, out_w), dtype=out_dtype, device=images.device)
+    nbytes = lib.b200_input_workspace_bytes(n, sh, sw, out_h, out_w)
+    if nbytes == 0:
+        raise B200Error("invalid input-stage geometry")
+    ws = workspace(images.device, nbytes, "input")
+    mean3 = (_f32 * 3)(*[float(v) for v in mean])
+    std3 = (_f32 * 3)(*[float(v) for v in std])
+    s = stats.begin("input")
+    _check(lib.b200_input_crop_resize_flip_norm(_ptr(images), _ptr(boxes), _ptr(flips), _ptr(out), _ptr(ws), ws.numel(),
+                                                n, sh, sw, out_h, out_w, mean3, std3,
+                                                F32 if out_dtype == torch.float32 else BF16, layout, _stream()),
+           "b200_input_crop_resize_flip_norm")
+    stats.end("input", 2, s, n * 3 * out_h * out_w * out.element_size())  # + box bytes, added by the caller
+    return out

@@ -1,0 +1,589 @@
+// K2: BatchNorm2d (+ residual add) + ReLU, forward (train / eval) and backward, on channels-last
+// rows [M = N*H*W, C].
+// Reference sites: torchvision resnet.py:93-103,147-161,240-243,269-270 (bn, relu, `out += identity`);
+// arithmetic torch/nn/modules/batchnorm.py:160-206; gradients = batch_norm_backward +
+// threshold_backward + the add's fan-out, executed by loss.backward() (imagenet.py:128).
+//
+// All kernels are HBM-bound streams over the activation:
+//   fwd train : stats pass reads x (1 E) ; apply pass reads x (+z) and writes y (2-3 E)
+//   bwd       : reduce pass reads dy,x (2 E) ; apply pass reads dy,x and writes dx (+dz) (3-4 E)
+// plus O(C * chunks) floats of partial sums.  Layout of the work: a CTA of 256 threads is
+// TX channel-vectors wide (a vector = VEC consecutive channels = one 8/16-byte access) and
+// TY = 256/TX rows tall, so a warp always touches >= 256 contiguous bytes; each thread keeps its
+// channels' constants in registers and walks down the rows of its chunk with U independent vector
+// loads in flight per tensor.  Per-thread partial sums are combined with warp shuffles (lanes that
+// share a channel), staged through shared memory across warps, and written as one partial per
+// (channel, chunk); a one-warp-per-channel finalize kernel folds the chunks.  The grid is
+// (channel tiles) x (row chunks) ~= 148 SMs x 8.
+//
+// Variance: each chunk accumulates sums shifted by the chunk's first row (sum(x-K), sum((x-K)^2)),
+// converts to (mean_b, M2_b) and the finalize combines chunks with the pairwise-update formula
+// (M2 = sum M2_b + n_b (mean_b - mean)^2), so there is no E[x^2]-E[x]^2 cancellation.
+#include "common.cuh"
+
+namespace {
+
+constexpr int kThreads = 256;
+constexpr int kWarps = kThreads / 32;
+
+// tuning knobs (b200_tune_set)
+int g_bn_target_ctas = B200_SM_COUNT * 8;
+int g_bn_vec_bf16 = 8;
+int g_bn_stats_reverse = 1;  // stats/reduce passes walk chunks back to front (tail of the producer's
+                             // output is the part most likely still in L2), apply passes front to back
+int g_bn_apply_reverse = 0;
+
+template <typename T, int VEC>
+struct Unroll {
+    static constexpr int U = (32 / (VEC * (int)sizeof(T))) < 1 ? 1 : (32 / (VEC * (int)sizeof(T)));
+};
+
+struct Geom {
+    int cv;          // channel vectors per row
+    int txl;         // log2(TX)
+    int tiles;       // channel tiles = cv / TX
+    int nchunk;      // row chunks
+    int64_t rpc;     // rows per chunk
+};
+
+Geom make_geom(int64_t m, int c, int vec, int unroll) {
+    Geom g;
+    g.cv = c / vec;
+    int tx = 1, l = 0;
+    while (tx < 32 && (g.cv % (tx * 2)) == 0) { tx *= 2; ++l; }
+    g.txl = l;
+    g.tiles = g.cv / tx;
+    const int ty = kThreads / tx;
+    const int64_t step = (int64_t)ty * unroll;
+    const int64_t max_chunks = (m + step - 1) / step;
+    int64_t want = g_bn_target_ctas / g.tiles;
+    if (want < 1) want = 1;
+    if (want > max_chunks) want = max_chunks;
+    int64_t rpc = (m + want - 1) / want;
+    rpc = (rpc + step - 1) / step * step;
+    g.rpc = rpc;
+    g.nchunk = (int)((m + rpc - 1) / rpc);
+    return g;
+}
+
+// Sum `val[0..NV)` over the threads of the CTA that share a channel vector.  On return threads with
+// threadIdx.x < TX hold the CTA totals of their channel vector.
+template <int NV>
+__device__ __forceinline__ void cta_reduce_rows(float (&val)[NV], int tx, float *smem /*[kWarps][32][NV]*/) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+    for (int k = 0; k < NV; ++k)
+        for (int o = 16; o >= tx; o >>= 1) val[k] += __shfl_xor_sync(0xffffffffu, val[k], o);
+    // with tx < 32 every warp covers all TX channel vectors; with tx == 32 likewise (one row per warp)
+    if (lane < tx) {
+#pragma unroll
+        for (int k = 0; k < NV; ++k) smem[(warp * 32 + lane) * NV + k] = val[k];
+    }
+    __syncthreads();
+    if (threadIdx.x < tx) {
+#pragma unroll
+        for (int k = 0; k < NV; ++k) {
+            float s = 0.f;
+#pragma unroll
+            for (int w = 0; w < kWarps; ++w) s += smem[(w * 32 + threadIdx.x) * NV + k];
+            val[k] = s;
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// forward pass 1: per-(channel, chunk) mean and M2
+template <typename T, int VEC>
+__global__ void __launch_bounds__(kThreads)
+bn_stats_kernel(const T *__restrict__ x, float2 *__restrict__ partial, int64_t m, int c, int txl, int nchunk,
+                int64_t rpc, int reverse) {
+    constexpr int U = Unroll<T, VEC>::U;
+    __shared__ float smem[kWarps * 32 * 2 * VEC];
+    const int tx = 1 << txl, ty = kThreads >> txl;
+    const int txi = threadIdx.x & (tx - 1), tyi = threadIdx.x >> txl;
+    const int cvi = blockIdx.x * tx + txi;
+    const int chunk = reverse ? (nchunk - 1 - (int)blockIdx.y) : (int)blockIdx.y;
+    const int64_t r0 = (int64_t)chunk * rpc;
+    const int64_t r1 = (r0 + rpc < m) ? (r0 + rpc) : m;
+    const T *xp = x + (int64_t)cvi * VEC;
+    float sh[VEC];
+    VecIO<T, VEC>::load(xp + r0 * c, sh);
+    float acc[2 * VEC];
+#pragma unroll
+    for (int k = 0; k < 2 * VEC; ++k) acc[k] = 0.f;
+    for (int64_t r = r0 + tyi; r < r1; r += (int64_t)ty * U) {
+        float v[U][VEC];
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const int64_t rr = r + (int64_t)u * ty;
+            if (rr < r1) {
+                VecIO<T, VEC>::load(xp + rr * c, v[u]);
+            } else {
+#pragma unroll
+                for (int k = 0; k < VEC; ++k) v[u][k] = sh[k];
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < U; ++u)
+#pragma unroll
+            for (int k = 0; k < VEC; ++k) {
+                const float d = v[u][k] - sh[k];
+                acc[k] += d;
+                acc[VEC + k] = fmaf(d, d, acc[VEC + k]);
+            }
+    }
+    cta_reduce_rows<2 * VEC>(acc, tx, smem);
+    if (threadIdx.x < tx) {
+        const float nb = (float)(r1 - r0);
+#pragma unroll
+        for (int k = 0; k < VEC; ++k) {
+            const float s1 = acc[k], s2 = acc[VEC + k];
+            const float mean_b = sh[k] + s1 / nb;
+            const float m2_b = fmaxf(s2 - s1 * s1 / nb, 0.f);
+            partial[(int64_t)(cvi * VEC + k) * nchunk + chunk] = make_float2(mean_b, m2_b);
+        }
+    }
+}
+
+// forward pass 2: one warp per channel folds the chunks, updates the running statistics and
+// writes saved = {mean, invstd, scale, shift}
+__global__ void __launch_bounds__(kThreads)
+bn_fwd_finalize_kernel(const float2 *__restrict__ partial, int nchunk, int64_t rpc, int64_t m, int c,
+                       const float *__restrict__ gamma, const float *__restrict__ beta, float *__restrict__ rmean,
+                       float *__restrict__ rvar, int64_t *__restrict__ nbt, float *__restrict__ saved, float eps,
+                       float momentum) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int ch = blockIdx.x * kWarps + warp;
+    if (blockIdx.x == 0 && threadIdx.x == 0 && nbt) *nbt += 1;
+    if (ch >= c) return;
+    const float2 *p = partial + (int64_t)ch * nchunk;
+    const float last_n = (float)(m - (int64_t)(nchunk - 1) * rpc);
+    float s = 0.f;
+    for (int i = lane; i < nchunk; i += 32) s = fmaf(i == nchunk - 1 ? last_n : (float)rpc, p[i].x, s);
+    s = warp_sum(s);
+    const float mean = s / (float)m;
+    float q = 0.f;
+    for (int i = lane; i < nchunk; i += 32) {
+        const float2 v = p[i];
+        const float d = v.x - mean;
+        q += fmaf(i == nchunk - 1 ? last_n : (float)rpc, d * d, v.y);
+    }
+    q = warp_sum(q);
+    if (lane == 0) {
+        const float var = q / (float)m;
+        const float invstd = 1.0f / sqrtf(var + eps);
+        const float sc = gamma[ch] * invstd;
+        saved[ch] = mean;
+        saved[c + ch] = invstd;
+        saved[2 * c + ch] = sc;
+        saved[3 * c + ch] = fmaf(-mean, sc, beta[ch]);
+        if (rmean) rmean[ch] = fmaf(momentum, mean, (1.f - momentum) * rmean[ch]);
+        if (rvar) rvar[ch] = fmaf(momentum, q / (float)(m - 1), (1.f - momentum) * rvar[ch]);
+    }
+}
+
+// forward pass 3 (and the whole of eval mode): y = act(x*scale + shift [+ z])
+template <typename T, int VEC, int ACT, bool EVAL>
+__global__ void __launch_bounds__(kThreads)
+bn_apply_kernel(const T *__restrict__ x, const T *__restrict__ z, T *__restrict__ y, uint8_t *__restrict__ mask,
+                const float *__restrict__ saved, const float *__restrict__ gamma, const float *__restrict__ beta,
+                const float *__restrict__ rmean, const float *__restrict__ rvar, float eps, int64_t m, int c, int txl,
+                int nchunk, int64_t rpc, int reverse) {
+    constexpr int U = Unroll<T, VEC>::U;
+    const int tx = 1 << txl, ty = kThreads >> txl;
+    const int txi = threadIdx.x & (tx - 1), tyi = threadIdx.x >> txl;
+    const int cvi = blockIdx.x * tx + txi;
+    const int cv = c / VEC;
+    const int chunk = reverse ? (nchunk - 1 - (int)blockIdx.y) : (int)blockIdx.y;
+    const int64_t r0 = (int64_t)chunk * rpc;
+    const int64_t r1 = (r0 + rpc < m) ? (r0 + rpc) : m;
+    const int64_t coff = (int64_t)cvi * VEC;
+    float sc[VEC], sf[VEC];
+#pragma unroll
+    for (int k = 0; k < VEC; ++k) {
+        const int ch = cvi * VEC + k;
+        if (EVAL) {
+            const float invstd = 1.0f / sqrtf(rvar[ch] + eps);
+            sc[k] = gamma[ch] * invstd;
+            sf[k] = fmaf(-rmean[ch], sc[k], beta[ch]);
+        } else {
+            sc[k] = saved[2 * c + ch];
+            sf[k] = saved[3 * c + ch];
+        }
+    }
+    for (int64_t r = r0 + tyi; r < r1; r += (int64_t)ty * U) {
+        float v[U][VEC], w[U][VEC];
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const int64_t rr = r + (int64_t)u * ty;
+            if (rr < r1) {
+                VecIO<T, VEC>::load_stream(x + rr * c + coff, v[u]);
+                if (ACT == B200_ACT_ADD_RELU) VecIO<T, VEC>::load_stream(z + rr * c + coff, w[u]);
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const int64_t rr = r + (int64_t)u * ty;
+            if (rr < r1) {
+                unsigned bits = 0;
+#pragma unroll
+                for (int k = 0; k < VEC; ++k) {
+                    float pre = fmaf(v[u][k], sc[k], sf[k]);
+                    if (ACT == B200_ACT_ADD_RELU) pre += w[u][k];
+                    if (ACT != B200_ACT_NONE) {
+                        bits |= (pre > 0.f ? 1u : 0u) << k;
+                        pre = fmaxf(pre, 0.f);
+                    }
+                    v[u][k] = pre;
+                }
+                VecIO<T, VEC>::store(y + rr * c + coff, v[u]);
+                if (ACT == B200_ACT_ADD_RELU && mask) mask[rr * cv + cvi] = (uint8_t)bits;
+            }
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// backward pass 1: per-(channel, chunk) sum(dyh) and sum(dyh * (x - mean))
+template <typename T, int VEC, int ACT>
+__global__ void __launch_bounds__(kThreads)
+bn_bwd_reduce_kernel(const T *__restrict__ dy, const T *__restrict__ x, const uint8_t *__restrict__ mask,
+                     const float *__restrict__ saved, float2 *__restrict__ partial, int64_t m, int c, int txl,
+                     int nchunk, int64_t rpc, int reverse) {
+    constexpr int U = Unroll<T, VEC>::U;
+    __shared__ float smem[kWarps * 32 * 2 * VEC];
+    const int tx = 1 << txl, ty = kThreads >> txl;
+    const int txi = threadIdx.x & (tx - 1), tyi = threadIdx.x >> txl;
+    const int cvi = blockIdx.x * tx + txi;
+    const int cv = c / VEC;
+    const int chunk = reverse ? (nchunk - 1 - (int)blockIdx.y) : (int)blockIdx.y;
+    const int64_t r0 = (int64_t)chunk * rpc;
+    const int64_t r1 = (r0 + rpc < m) ? (r0 + rpc) : m;
+    const int64_t coff = (int64_t)cvi * VEC;
+    float mean[VEC], sc[VEC], sf[VEC];
+#pragma unroll
+    for (int k = 0; k < VEC; ++k) {
+        const int ch = cvi * VEC + k;
+        mean[k] = saved[ch];
+        if (ACT == B200_ACT_RELU) { sc[k] = saved[2 * c + ch]; sf[k] = saved[3 * c + ch]; }
+    }
+    float acc[2 * VEC];
+#pragma unroll
+    for (int k = 0; k < 2 * VEC; ++k) acc[k] = 0.f;
+    for (int64_t r = r0 + tyi; r < r1; r += (int64_t)ty * U) {
+        float g[U][VEC], v[U][VEC];
+        unsigned bits[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const int64_t rr = r + (int64_t)u * ty;
+            if (rr < r1) {
+                VecIO<T, VEC>::load(dy + rr * c + coff, g[u]);
+                VecIO<T, VEC>::load(x + rr * c + coff, v[u]);
+                if (ACT == B200_ACT_ADD_RELU) bits[u] = mask[rr * cv + cvi];
+            } else {
+#pragma unroll
+                for (int k = 0; k < VEC; ++k) { g[u][k] = 0.f; v[u][k] = mean[k]; }
+                bits[u] = 0;
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < U; ++u)
+#pragma unroll
+            for (int k = 0; k < VEC; ++k) {
+                float gk = g[u][k];
+                if (ACT == B200_ACT_RELU) gk = fmaf(v[u][k], sc[k], sf[k]) > 0.f ? gk : 0.f;
+                if (ACT == B200_ACT_ADD_RELU) gk = ((bits[u] >> k) & 1u) ? gk : 0.f;
+                acc[k] += gk;
+                acc[VEC + k] = fmaf(gk, v[u][k] - mean[k], acc[VEC + k]);
+            }
+    }
+    cta_reduce_rows<2 * VEC>(acc, tx, smem);
+    if (threadIdx.x < tx) {
+#pragma unroll
+        for (int k = 0; k < VEC; ++k)
+            partial[(int64_t)(cvi * VEC + k) * nchunk + chunk] = make_float2(acc[k], acc[VEC + k]);
+    }
+}
+
+// backward pass 2: fold chunks; dgamma, dbeta; coefficients of dx = c0*dyh + c1*(x-mean) + c2
+__global__ void __launch_bounds__(kThreads)
+bn_bwd_finalize_kernel(const float2 *__restrict__ partial, int nchunk, int64_t m, int c,
+                       const float *__restrict__ gamma, const float *__restrict__ saved, float *__restrict__ dgamma,
+                       float *__restrict__ dbeta, float *__restrict__ coef) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int ch = blockIdx.x * kWarps + warp;
+    if (ch >= c) return;
+    const float2 *p = partial + (int64_t)ch * nchunk;
+    float a = 0.f, b = 0.f;
+    for (int i = lane; i < nchunk; i += 32) {
+        const float2 v = p[i];
+        a += v.x;
+        b += v.y;
+    }
+    a = warp_sum(a);
+    b = warp_sum(b);
+    if (lane == 0) {
+        const float invstd = saved[c + ch];
+        const float gs = gamma[ch] * invstd;
+        const float inv_m = 1.0f / (float)m;
+        const float ps = b * invstd * invstd * inv_m;
+        const float gm = a * inv_m;
+        if (dgamma) dgamma[ch] = b * invstd;
+        if (dbeta) dbeta[ch] = a;
+        coef[ch] = gs;
+        coef[c + ch] = -ps * gs;
+        coef[2 * c + ch] = -gm * gs;
+    }
+}
+
+// backward pass 3: dx (and dz) from dy, x
+template <typename T, int VEC, int ACT>
+__global__ void __launch_bounds__(kThreads)
+bn_bwd_apply_kernel(const T *__restrict__ dy, const T *__restrict__ x, const uint8_t *__restrict__ mask,
+                    const float *__restrict__ saved, const float *__restrict__ coef, T *__restrict__ dx,
+                    T *__restrict__ dz, int64_t m, int c, int txl, int nchunk, int64_t rpc, int reverse) {
+    constexpr int U = Unroll<T, VEC>::U;
+    const int tx = 1 << txl, ty = kThreads >> txl;
+    const int txi = threadIdx.x & (tx - 1), tyi = threadIdx.x >> txl;
+    const int cvi = blockIdx.x * tx + txi;
+    const int cv = c / VEC;
+    const int chunk = reverse ? (nchunk - 1 - (int)blockIdx.y) : (int)blockIdx.y;
+    const int64_t r0 = (int64_t)chunk * rpc;
+    const int64_t r1 = (r0 + rpc < m) ? (r0 + rpc) : m;
+    const int64_t coff = (int64_t)cvi * VEC;
+    float mean[VEC], c0[VEC], c1[VEC], c2[VEC], sc[VEC], sf[VEC];
+#pragma unroll
+    for (int k = 0; k < VEC; ++k) {
+        const int ch = cvi * VEC + k;
+        mean[k] = saved[ch];
+        c0[k] = coef[ch];
+        c1[k] = coef[c + ch];
+        c2[k] = coef[2 * c + ch];
+        if (ACT == B200_ACT_RELU) { sc[k] = saved[2 * c + ch]; sf[k] = saved[3 * c + ch]; }
+    }
+    for (int64_t r = r0 + tyi; r < r1; r += (int64_t)ty * U) {
+        float g[U][VEC], v[U][VEC];
+        unsigned bits[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const int64_t rr = r + (int64_t)u * ty;
+            if (rr < r1) {
+                VecIO<T, VEC>::load_stream(dy + rr * c + coff, g[u]);
+                VecIO<T, VEC>::load_stream(x + rr * c + coff, v[u]);
+                if (ACT == B200_ACT_ADD_RELU) bits[u] = mask[rr * cv + cvi];
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const int64_t rr = r + (int64_t)u * ty;
+            if (rr < r1) {
+#pragma unroll
+                for (int k = 0; k < VEC; ++k) {
+                    float gk = g[u][k];
+                    if (ACT == B200_ACT_RELU) gk = fmaf(v[u][k], sc[k], sf[k]) > 0.f ? gk : 0.f;
+                    if (ACT == B200_ACT_ADD_RELU) gk = ((bits[u] >> k) & 1u) ? gk : 0.f;
+                    g[u][k] = gk;
+                    v[u][k] = fmaf(gk, c0[k], fmaf(v[u][k] - mean[k], c1[k], c2[k]));
+                }
+                VecIO<T, VEC>::store(dx + rr * c + coff, v[u]);
+                if (ACT == B200_ACT_ADD_RELU) VecIO<T, VEC>::store(dz + rr * c + coff, g[u]);
+            }
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+struct Ws {
+    float2 *partial;
+    float *coef;
+};
+
+size_t ws_bytes_for(const Geom &g, int c) { return sizeof(float2) * (size_t)c * g.nchunk + sizeof(float) * 3 * (size_t)c + 64; }
+
+Ws carve(void *ws, const Geom &g, int c) {
+    Ws w;
+    w.partial = static_cast<float2 *>(ws);
+    size_t off = sizeof(float2) * (size_t)c * g.nchunk;
+    off = (off + 15) / 16 * 16;
+    w.coef = reinterpret_cast<float *>(static_cast<char *>(ws) + off);
+    return w;
+}
+
+template <typename T, int VEC>
+int fwd_train_impl(const void *x_, const void *z_, void *y_, uint8_t *mask, const float *gamma, const float *beta,
+                   float *rm, float *rv, int64_t *nbt, float *saved, void *ws, size_t ws_bytes, int64_t m, int c,
+                   float eps, float momentum, int act, cudaStream_t st) {
+    const T *x = static_cast<const T *>(x_);
+    const T *z = static_cast<const T *>(z_);
+    T *y = static_cast<T *>(y_);
+    const Geom g = make_geom(m, c, VEC, Unroll<T, VEC>::U);
+    if (ws_bytes < ws_bytes_for(g, c)) return (int)cudaErrorInvalidValue;
+    const Ws w = carve(ws, g, c);
+    const dim3 grid(g.tiles, g.nchunk);
+    bn_stats_kernel<T, VEC><<<grid, kThreads, 0, st>>>(x, w.partial, m, c, g.txl, g.nchunk, g.rpc, g_bn_stats_reverse);
+    B200_CHECK_LAUNCH();
+    bn_fwd_finalize_kernel<<<(c + kWarps - 1) / kWarps, kThreads, 0, st>>>(w.partial, g.nchunk, g.rpc, m, c, gamma, beta,
+                                                                          rm, rv, nbt, saved, eps, momentum);
+    B200_CHECK_LAUNCH();
+    const int rev = g_bn_apply_reverse;
+#define B200_APPLY(ACT)                                                                                         \
+    bn_apply_kernel<T, VEC, ACT, false><<<grid, kThreads, 0, st>>>(x, z, y, mask, saved, nullptr, nullptr, nullptr, \
+                                                                   nullptr, eps, m, c, g.txl, g.nchunk, g.rpc, rev)
+    if (act == B200_ACT_NONE) B200_APPLY(B200_ACT_NONE);
+    else if (act == B200_ACT_RELU) B200_APPLY(B200_ACT_RELU);
+    else B200_APPLY(B200_ACT_ADD_RELU);
+#undef B200_APPLY
+    B200_CHECK_LAUNCH();
+    return 0;
+}
+
+template <typename T, int VEC>
+int fwd_eval_impl(const void *x_, const void *z_, void *y_, const float *gamma, const float *beta, const float *rm,
+                  const float *rv, int64_t m, int c, float eps, int act, cudaStream_t st) {
+    const T *x = static_cast<const T *>(x_);
+    const T *z = static_cast<const T *>(z_);
+    T *y = static_cast<T *>(y_);
+    const Geom g = make_geom(m, c, VEC, Unroll<T, VEC>::U);
+    const dim3 grid(g.tiles, g.nchunk);
+#define B200_APPLY(ACT)                                                                                      \
+    bn_apply_kernel<T, VEC, ACT, true><<<grid, kThreads, 0, st>>>(x, z, y, nullptr, nullptr, gamma, beta, rm, rv, \
+                                                                  eps, m, c, g.txl, g.nchunk, g.rpc, 0)
+    if (act == B200_ACT_NONE) B200_APPLY(B200_ACT_NONE);
+    else if (act == B200_ACT_RELU) B200_APPLY(B200_ACT_RELU);
+    else B200_APPLY(B200_ACT_ADD_RELU);
+#undef B200_APPLY
+    B200_CHECK_LAUNCH();
+    return 0;
+}
+
+template <typename T, int VEC>
+int bwd_impl(const void *dy_, const void *x_, const uint8_t *mask, const float *gamma, const float *saved, void *dx_,
+             void *dz_, float *dgamma, float *dbeta, void *ws, size_t ws_bytes, int64_t m, int c, int act,
+             cudaStream_t st) {
+    const T *dy = static_cast<const T *>(dy_);
+    const T *x = static_cast<const T *>(x_);
+    T *dx = static_cast<T *>(dx_);
+    T *dz = static_cast<T *>(dz_);
+    const Geom g = make_geom(m, c, VEC, Unroll<T, VEC>::U);
+    if (ws_bytes < ws_bytes_for(g, c)) return (int)cudaErrorInvalidValue;
+    const Ws w = carve(ws, g, c);
+    const dim3 grid(g.tiles, g.nchunk);
+    const int rrev = g_bn_stats_reverse, arev = g_bn_apply_reverse;
+#define B200_BWD(ACT)                                                                                            \
+    do {                                                                                                         \
+        bn_bwd_reduce_kernel<T, VEC, ACT><<<grid, kThreads, 0, st>>>(dy, x, mask, saved, w.partial, m, c, g.txl,     \
+                                                                     g.nchunk, g.rpc, rrev);                     \
+        B200_CHECK_LAUNCH();                                                                                     \
+        bn_bwd_finalize_kernel<<<(c + kWarps - 1) / kWarps, kThreads, 0, st>>>(w.partial, g.nchunk, m, c, gamma,  \
+                                                                              saved, dgamma, dbeta, w.coef);    \
+        B200_CHECK_LAUNCH();                                                                                     \
+        bn_bwd_apply_kernel<T, VEC, ACT><<<grid, kThreads, 0, st>>>(dy, x, mask, saved, w.coef, dx, dz, m, c, g.txl, \
+                                                                    g.nchunk, g.rpc, arev);                      \
+        B200_CHECK_LAUNCH();                                                                                     \
+    } while (0)
+    if (act == B200_ACT_NONE) B200_BWD(B200_ACT_NONE);
+    else if (act == B200_ACT_RELU) B200_BWD(B200_ACT_RELU);
+    else B200_BWD(B200_ACT_ADD_RELU);
+#undef B200_BWD
+    return 0;
+}
+
+int check_common(int64_t m, int c, int act, int dtype, int vec) {
+    if (m < 1 || c < 1) return (int)cudaErrorInvalidValue;
+    if (act < B200_ACT_NONE || act > B200_ACT_ADD_RELU) return (int)cudaErrorInvalidValue;
+    if (dtype != B200_F32 && dtype != B200_BF16) return (int)cudaErrorInvalidValue;
+    if (c % vec != 0) return (int)cudaErrorInvalidValue;
+    return 0;
+}
+
+}  // namespace
+
+extern "C" int b200_bn_vec(int dtype) { return dtype == B200_BF16 ? g_bn_vec_bf16 : 4; }
+
+extern "C" int b200_tune_set(const char *key, int value) {
+    if (!key) return (int)cudaErrorInvalidValue;
+    auto eq = [&](const char *s) { const char *a = key; while (*a && *a == *s) { ++a; ++s; } return *a == *s; };
+    if (eq("bn_target_ctas")) { if (value < 1) return (int)cudaErrorInvalidValue; g_bn_target_ctas = value; return 0; }
+    if (eq("bn_vec_bf16")) { if (value != 4 && value != 8) return (int)cudaErrorInvalidValue; g_bn_vec_bf16 = value; return 0; }
+    if (eq("bn_stats_reverse")) { g_bn_stats_reverse = value != 0; return 0; }
+    if (eq("bn_apply_reverse")) { g_bn_apply_reverse = value != 0; return 0; }
+    return (int)cudaErrorInvalidValue;
+}
+
+extern "C" size_t b200_bn_workspace_bytes(int64_t m, int c, int dtype) {
+    if (m < 1 || c < 1) return 0;
+    // upper bound over both vector widths and any tuning of the chunk count
+    size_t best = 0;
+    const int vecs[2] = {4, 8};
+    for (int i = 0; i < 2; ++i) {
+        const int vec = vecs[i];
+        if (dtype != B200_BF16 && vec == 8) continue;
+        if (c % vec) continue;
+        const int unroll = dtype == B200_BF16 ? (vec == 8 ? 2 : 4) : 2;
+        const Geom g = make_geom(m, c, vec, unroll);
+        const size_t b = ws_bytes_for(g, c);
+        if (b > best) best = b;
+    }
+    return best;
+}
+
+extern "C" int b200_bn_fwd_train(const void *x, const void *z, void *y, uint8_t *mask, const float *gamma,
+                                 const float *beta, float *running_mean, float *running_var,
+                                 int64_t *num_batches_tracked, float *saved, void *workspace, size_t workspace_bytes,
+                                 int64_t m, int c, float eps, float momentum, int act, int dtype, void *stream) {
+    const int vec = b200_bn_vec(dtype);
+    int e = check_common(m, c, act, dtype, vec);
+    if (e) return e;
+    if (m < 2) return (int)cudaErrorInvalidValue;  // "Expected more than 1 value per channel when training"
+    if (!x || !y || !gamma || !beta || !saved || !workspace) return (int)cudaErrorInvalidValue;
+    if (act == B200_ACT_ADD_RELU && !z) return (int)cudaErrorInvalidValue;
+    if (b200_misaligned(x) || b200_misaligned(y) || b200_misaligned(z) || b200_misaligned(workspace))
+        return (int)cudaErrorMisalignedAddress;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    if (dtype == B200_F32)
+        return fwd_train_impl<float, 4>(x, z, y, mask, gamma, beta, running_mean, running_var, num_batches_tracked, saved,
+                                        workspace, workspace_bytes, m, c, eps, momentum, act, st);
+    if (vec == 8)
+        return fwd_train_impl<__nv_bfloat16, 8>(x, z, y, mask, gamma, beta, running_mean, running_var,
+                                                num_batches_tracked, saved, workspace, workspace_bytes, m, c, eps,
+                                                momentum, act, st);
+    return fwd_train_impl<__nv_bfloat16, 4>(x, z, y, mask, gamma, beta, running_mean, running_var, num_batches_tracked,
+                                            saved, workspace, workspace_bytes, m, c, eps, momentum, act, st);
+}
+
+extern "C" int b200_bn_fwd_eval(const void *x, const void *z, void *y, const float *gamma, const float *beta,
+                                const float *running_mean, const float *running_var, int64_t m, int c, float eps,
+                                int act, int dtype, void *stream) {
+    const int vec = b200_bn_vec(dtype);
+    int e = check_common(m, c, act, dtype, vec);
+    if (e) return e;
+    if (!x || !y || !gamma || !beta || !running_mean || !running_var) return (int)cudaErrorInvalidValue;
+    if (act == B200_ACT_ADD_RELU && !z) return (int)cudaErrorInvalidValue;
+    if (b200_misaligned(x) || b200_misaligned(y) || b200_misaligned(z)) return (int)cudaErrorMisalignedAddress;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    if (dtype == B200_F32) return fwd_eval_impl<float, 4>(x, z, y, gamma, beta, running_mean, running_var, m, c, eps, act, st);
+    if (vec == 8)
+        return fwd_eval_impl<__nv_bfloat16, 8>(x, z, y, gamma, beta, running_mean, running_var, m, c, eps, act, st);
+    return fwd_eval_impl<__nv_bfloat16, 4>(x, z, y, gamma, beta, running_mean, running_var, m, c, eps, act, st);
+}
+
+extern "C" int b200_bn_bwd(const void *dy, const void *x, const uint8_t *mask, const float *gamma, const float *saved,
+                           void *dx, void *dz, float *dgamma, float *dbeta, void *workspace, size_t workspace_bytes,
+                           int64_t m, int c, int act, int dtype, void *stream) {
+    const int vec = b200_bn_vec(dtype);
+    int e = check_common(m, c, act, dtype, vec);
+    if (e) return e;
+    if (!dy || !x || !gamma || !saved || !dx || !workspace) return (int)cudaErrorInvalidValue;
+    if (act == B200_ACT_ADD_RELU && (!mask || !dz)) return (int)cudaErrorInvalidValue;
+    if (b200_misaligned(dy) || b200_misaligned(x) || b200_misaligned(dx) || b200_misaligned(dz) ||
+        b200_misaligned(workspace))
+        return (int)cudaErrorMisalignedAddress;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    if (dtype == B200_F32)
+        return bwd_impl<float, 4>(dy, x, mask, gamma, saved, dx, dz, dgamma, dbeta, workspace, workspace_bytes, m, c, act, st);
+    if (vec == 8)
+        return bwd_impl<__nv_bfloat16, 8>(dy, x, mask, gamma, saved, dx, dz, dgamma, dbeta, workspace, workspace_bytes, m,
+                                          c, act, st);
+    return bwd_impl<__nv_bfloat16, 4>(dy, x, mask, gamma, saved, dx, dz, dgamma, dbeta, workspace, workspace_bytes, m, c,
+                                      act, st);
+}

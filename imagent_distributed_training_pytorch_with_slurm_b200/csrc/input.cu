@@ -1,0 +1,240 @@
+// K1: input stage.  uint8 NHWC batch -> per-sample crop box -> Pillow-exact antialiased bilinear
+// resize -> horizontal flip -> ToTensor (/255) -> Normalize ((x-mean)/std) -> bf16/f32, one pass.
+// Reference sites: transforms.Compose([Resize((448,448)), ToTensor(), Normalize(.5,.5)])
+// (imagenet.py:280-283) executed per image on PIL images inside the DataLoader workers
+// (imagenet.py:350-354); north-star mode adds torchvision RandomResizedCrop/RandomHorizontalFlip
+// (transforms.py:928-981,712-722), whose PIL path is crop -> the same resize -> flip.
+//
+// The resize follows Pillow's ImagingResample for 8-bit images (Resample.c, BILINEAR):
+//   precompute_coeffs   : double-precision triangle weights, support = max(scale,1), normalised
+//   normalize_coeffs_8bpc: fixed point, 22 fractional bits, round half up
+//   horizontal pass     : clip8((2^21 + sum pix*k) >> 22) into an 8-bit intermediate
+//   vertical pass       : the same on the intermediate
+// All double arithmetic uses the round-to-nearest intrinsics so that no multiply-add is contracted
+// and the integer coefficients equal Pillow's bit for bit.
+//
+// HBM traffic: the crop box is read once (neighbouring tiles re-read a few rows out of L2), the
+// output is written once; the normalisation is a 3x256 float look-up table in shared memory
+// because the resized pixel is an 8-bit value.
+#include "common.cuh"
+
+namespace {
+
+constexpr int kThreads = 256;
+constexpr int kPrecisionBits = 32 - 8 - 2;
+constexpr int kTileRows = 8;
+
+__host__ __device__ inline int ksize_for(int src, int out) {
+    // ceil(max(src/out, 1)) * 2 + 1, in integers
+    int s = (src + out - 1) / out;
+    if (s < 1) s = 1;
+    return s * 2 + 1;
+}
+
+__device__ __forceinline__ double tri_weight(double x) {
+    if (x < 0.0) x = -x;
+    return x < 1.0 ? __dsub_rn(1.0, x) : 0.0;
+}
+
+// tables per sample: bounds_x[out_w][2], coef_x[out_w][KX], bounds_y[out_h][2], coef_y[out_h][KY]
+__global__ void __launch_bounds__(kThreads)
+input_coeff_kernel(const int32_t *__restrict__ boxes, int64_t n, int out_h, int out_w, int KX, int KY,
+                   int32_t *__restrict__ ws) {
+    const int per_row = out_w + out_h;
+    const int64_t gid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (gid >= n * per_row) return;
+    const int64_t s = gid / per_row;
+    const int idx = (int)(gid - s * per_row);
+    const bool vertical = idx >= out_w;
+    const int xx = vertical ? idx - out_w : idx;
+    const int in_size = vertical ? boxes[s * 4 + 2] : boxes[s * 4 + 3];
+    const int out_size = vertical ? out_h : out_w;
+    const int K = vertical ? KY : KX;
+    const int64_t per_sample = (int64_t)out_w * (2 + KX) + (int64_t)out_h * (2 + KY);
+    int32_t *base = ws + s * per_sample;
+    int32_t *bounds = vertical ? base + (int64_t)out_w * (2 + KX) : base;
+    int32_t *coef = bounds + 2 * out_size;
+
+    const double scale = __ddiv_rn((double)in_size, (double)out_size);
+    const double fs = scale < 1.0 ? 1.0 : scale;
+    const double support = fs;  // bilinear support 1.0 * filterscale
+    const double center = __dmul_rn(__dadd_rn((double)xx, 0.5), scale);
+    int lo = __double2int_rz(__dadd_rn(__dsub_rn(center, support), 0.5));
+    if (lo < 0) lo = 0;
+    int hi = __double2int_rz(__dadd_rn(__dadd_rn(center, support), 0.5));
+    if (hi > in_size) hi = in_size;
+    int cnt = hi - lo;
+    if (cnt > K) cnt = K;  // cannot happen for boxes inside the image; keeps the table in bounds
+    if (cnt < 0) cnt = 0;
+    const double ss = __ddiv_rn(1.0, fs);
+    double ww = 0.0;
+    for (int x = 0; x < cnt; ++x)
+        ww = __dadd_rn(ww, tri_weight(__dmul_rn(__dadd_rn(__dsub_rn((double)(x + lo), center), 0.5), ss)));
+    for (int x = 0; x < K; ++x) {
+        int kk = 0;
+        if (x < cnt) {
+            double w = tri_weight(__dmul_rn(__dadd_rn(__dsub_rn((double)(x + lo), center), 0.5), ss));
+            if (ww != 0.0) w = __ddiv_rn(w, ww);
+            kk = __double2int_rz(__dadd_rn(0.5, __dmul_rn(w, (double)(1 << kPrecisionBits))));
+        }
+        coef[(int64_t)xx * K + x] = kk;
+    }
+    bounds[2 * xx] = lo;
+    bounds[2 * xx + 1] = cnt;
+}
+
+__device__ __forceinline__ int clip8(int acc) {
+    int v = acc >> kPrecisionBits;
+    return v < 0 ? 0 : (v > 255 ? 255 : v);
+}
+
+template <typename OutT>
+__device__ __forceinline__ OutT cast_out(float v);
+template <>
+__device__ __forceinline__ float cast_out<float>(float v) { return v; }
+template <>
+__device__ __forceinline__ __nv_bfloat16 cast_out<__nv_bfloat16>(float v) { return __float2bfloat16_rn(v); }
+
+struct Norm { float mean[3]; float std[3]; };
+
+template <typename OutT>
+__global__ void __launch_bounds__(kThreads)
+input_resample_kernel(const uint8_t *__restrict__ images, const int32_t *__restrict__ boxes,
+                      const uint8_t *__restrict__ flips, OutT *__restrict__ out, const int32_t *__restrict__ ws,
+                      int src_h, int src_w, int out_h, int out_w, int KX, int KY, int max_src_rows, Norm nrm,
+                      int layout) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    float *lut = reinterpret_cast<float *>(smem_raw);          // [3][256]
+    uint8_t *inter = smem_raw + 3 * 256 * sizeof(float);       // [max_src_rows][out_w][3]
+
+    const int64_t s = blockIdx.y;
+    const int y0 = blockIdx.x * kTileRows;
+    const int y1 = (y0 + kTileRows < out_h) ? y0 + kTileRows : out_h;
+    for (int i = threadIdx.x; i < 3 * 256; i += kThreads) {
+        const int ch = i >> 8, v = i & 255;
+        // ToTensor: float32(v) / 255 ; Normalize: (x - mean) / std, all IEEE float32
+        lut[i] = __fdiv_rn(__fsub_rn(__fdiv_rn((float)v, 255.0f), nrm.mean[ch]), nrm.std[ch]);
+    }
+    const int64_t per_sample = (int64_t)out_w * (2 + KX) + (int64_t)out_h * (2 + KY);
+    const int32_t *bx = ws + s * per_sample;
+    const int32_t *cx = bx + 2 * out_w;
+    const int32_t *by = bx + (int64_t)out_w * (2 + KX);
+    const int32_t *cy = by + 2 * out_h;
+    const int top = boxes[s * 4 + 0], left = boxes[s * 4 + 1];
+    const bool flip = flips && flips[s] != 0;
+    const int ylo = by[2 * y0];
+    const int nrows = by[2 * (y1 - 1)] + by[2 * (y1 - 1) + 1] - ylo;
+    if (nrows > max_src_rows) return;  // contract violation (box outside the stated limits)
+
+    // horizontal pass: needed source rows -> 8-bit intermediate in shared memory
+    const uint8_t *img = images + ((int64_t)s * src_h + top + ylo) * (int64_t)src_w * 3 + (int64_t)left * 3;
+    for (int idx = threadIdx.x; idx < nrows * out_w; idx += kThreads) {
+        const int rr = idx / out_w, xx = idx - rr * out_w;
+        const int xmin = bx[2 * xx], cnt = bx[2 * xx + 1];
+        const uint8_t *px = img + (int64_t)rr * src_w * 3 + xmin * 3;
+        const int32_t *k = cx + (int64_t)xx * KX;
+        int a0 = 1 << (kPrecisionBits - 1), a1 = a0, a2 = a0;
+        for (int t = 0; t < cnt; ++t) {
+            const int kk = k[t];
+            a0 += (int)px[3 * t + 0] * kk;
+            a1 += (int)px[3 * t + 1] * kk;
+            a2 += (int)px[3 * t + 2] * kk;
+        }
+        uint8_t *o = inter + (rr * out_w + xx) * 3;
+        o[0] = (uint8_t)clip8(a0);
+        o[1] = (uint8_t)clip8(a1);
+        o[2] = (uint8_t)clip8(a2);
+    }
+    __syncthreads();
+
+    // vertical pass -> flip -> normalise -> store
+    const int npix = (y1 - y0) * out_w;
+    for (int idx = threadIdx.x; idx < npix; idx += kThreads) {
+        const int ry = idx / out_w, xx = idx - ry * out_w;
+        const int yy = y0 + ry;
+        const int ymin = by[2 * yy] - ylo, cnt = by[2 * yy + 1];
+        const int32_t *k = cy + (int64_t)yy * KY;
+        int a0 = 1 << (kPrecisionBits - 1), a1 = a0, a2 = a0;
+        for (int t = 0; t < cnt; ++t) {
+            const int kk = k[t];
+            const uint8_t *p = inter + ((ymin + t) * out_w + xx) * 3;
+            a0 += (int)p[0] * kk;
+            a1 += (int)p[1] * kk;
+            a2 += (int)p[2] * kk;
+        }
+        const float f0 = lut[clip8(a0)], f1 = lut[256 + clip8(a1)], f2 = lut[512 + clip8(a2)];
+        const int xd = flip ? (out_w - 1 - xx) : xx;
+        if (layout == B200_LAYOUT_NHWC) {
+            OutT *o = out + (((int64_t)s * out_h + yy) * out_w + xd) * 3;
+            o[0] = cast_out<OutT>(f0);
+            o[1] = cast_out<OutT>(f1);
+            o[2] = cast_out<OutT>(f2);
+        } else {
+            const int64_t plane = (int64_t)out_h * out_w;
+            OutT *o = out + (int64_t)s * 3 * plane + (int64_t)yy * out_w + xd;
+            o[0] = cast_out<OutT>(f0);
+            o[plane] = cast_out<OutT>(f1);
+            o[2 * plane] = cast_out<OutT>(f2);
+        }
+    }
+}
+
+int max_src_rows_for(int src_h, int out_h) {
+    const double s = (double)src_h / (double)out_h;
+    const double sup = s < 1.0 ? 1.0 : s;
+    return (int)((kTileRows - 1) * s + 2.0 * sup + 1.0) + 2;
+}
+
+}  // namespace
+
+extern "C" size_t b200_input_workspace_bytes(int64_t n, int src_h, int src_w, int out_h, int out_w) {
+    if (n < 1 || src_h < 1 || src_w < 1 || out_h < 1 || out_w < 1) return 0;
+    const int KX = ksize_for(src_w, out_w), KY = ksize_for(src_h, out_h);
+    return sizeof(int32_t) * (size_t)n * ((size_t)out_w * (2 + KX) + (size_t)out_h * (2 + KY)) + 16;
+}
+
+extern "C" int b200_input_crop_resize_flip_norm(const uint8_t *images, const int32_t *boxes, const uint8_t *flips,
+                                                void *out, void *workspace, size_t workspace_bytes, int64_t n,
+                                                int src_h, int src_w, int out_h, int out_w, const float *mean3,
+                                                const float *std3, int out_dtype, int out_layout, void *stream) {
+    if (!images || !boxes || !out || !workspace || !mean3 || !std3) return (int)cudaErrorInvalidValue;
+    if (n < 1 || src_h < 1 || src_w < 1 || out_h < 1 || out_w < 1) return (int)cudaErrorInvalidValue;
+    if (out_dtype != B200_F32 && out_dtype != B200_BF16) return (int)cudaErrorInvalidValue;
+    if (out_layout != B200_LAYOUT_NHWC && out_layout != B200_LAYOUT_NCHW) return (int)cudaErrorInvalidValue;
+    if ((int64_t)src_h > 8 * (int64_t)out_h || (int64_t)src_w > 8 * (int64_t)out_w) return (int)cudaErrorInvalidValue;
+    if (n > 65535) return (int)cudaErrorInvalidValue;
+    if (workspace_bytes < b200_input_workspace_bytes(n, src_h, src_w, out_h, out_w)) return (int)cudaErrorInvalidValue;
+    if (b200_misaligned(workspace) || b200_misaligned(out, 4)) return (int)cudaErrorMisalignedAddress;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const int KX = ksize_for(src_w, out_w), KY = ksize_for(src_h, out_h);
+    int32_t *ws = static_cast<int32_t *>(workspace);
+    const int64_t items = n * (int64_t)(out_w + out_h);
+    input_coeff_kernel<<<(unsigned)((items + kThreads - 1) / kThreads), kThreads, 0, st>>>(boxes, n, out_h, out_w, KX,
+                                                                                           KY, ws);
+    B200_CHECK_LAUNCH();
+    const int max_rows = max_src_rows_for(src_h, out_h);
+    const size_t smem = 3 * 256 * sizeof(float) + (size_t)max_rows * out_w * 3;
+    if (smem > 200 * 1024) return (int)cudaErrorInvalidValue;
+    Norm nrm;
+    for (int i = 0; i < 3; ++i) { nrm.mean[i] = mean3[i]; nrm.std[i] = std3[i]; }
+    const dim3 grid((out_h + kTileRows - 1) / kTileRows, (unsigned)n);
+    if (out_dtype == B200_F32) {
+        auto kern = input_resample_kernel<float>;
+        if (smem > 48 * 1024) {
+            cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+            if (e != cudaSuccess) return (int)e;
+        }
+        kern<<<grid, kThreads, smem, st>>>(images, boxes, flips, static_cast<float *>(out), ws, src_h, src_w, out_h,
+                                           out_w, KX, KY, max_rows, nrm, out_layout);
+    } else {
+        auto kern = input_resample_kernel<__nv_bfloat16>;
+        if (smem > 48 * 1024) {
+            cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+            if (e != cudaSuccess) return (int)e;
+        }
+        kern<<<grid, kThreads, smem, st>>>(images, boxes, flips, static_cast<__nv_bfloat16 *>(out), ws, src_h, src_w,
+                                           out_h, out_w, KX, KY, max_rows, nrm, out_layout);
+    }
+    B200_CHECK_LAUNCH();
+    return 0;
+}

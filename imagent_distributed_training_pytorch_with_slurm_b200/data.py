@@ -1,0 +1,132 @@
+"""Input stage on the device, and synthetic ImageNet-shaped loaders.
+
+Replaces the reference's CPU transform pipeline ``Resize((448,448)) -> ToTensor -> Normalize(.5,.5)``
+run per image in 10 DataLoader workers (imagenet.py:280-283,350-354) plus the fp32 H2D copy
+(imagenet.py:119) by: uint8 NHWC batch -> (pinned) H2D -> ONE fused kernel doing crop box, Pillow-exact
+antialiased bilinear resize, flip, /255, (x-mean)/std and the cast to channels-last bf16.
+
+Two modes:
+  * reference mode  - box = whole image, no flip, 448x448, mean = std = 0.5 (what imagenet.py does);
+  * north-star mode - torchvision RandomResizedCrop(224) + RandomHorizontalFlip boxes/flips, drawn on
+    the host from a torch CPU generator in torchvision's order (transforms.py:928-981,712-722), and
+    ImageNet mean/std.
+"""
+import math
+
+import torch
+
+from . import _cabi
+
+IMAGENET_MEAN, IMAGENET_STD = (0.485, 0.456, 0.406), (0.229, 0.224, 0.225)
+REFERENCE_MEAN, REFERENCE_STD = (0.5, 0.5, 0.5), (0.5, 0.5, 0.5)
+
+
+_LOG_RATIO_CACHE = {}
+
+
+def _log_ratio32(ratio):
+    key = tuple(ratio)
+    if key not in _LOG_RATIO_CACHE:  # float32 bounds, as torchvision's torch.log(torch.tensor(ratio))
+        _LOG_RATIO_CACHE[key] = torch.log(torch.tensor(key, dtype=torch.float32)).tolist()
+    return _LOG_RATIO_CACHE[key]
+
+
+def rrc_params(height, width, scale=(0.08, 1.0), ratio=(3.0 / 4.0, 4.0 / 3.0), generator=None, _scratch=None):
+    """(top, left, h, w) with the draw order and rounding of torchvision's
+    ``RandomResizedCrop.get_params`` (transforms.py:928-973)."""
+    area = height * width
+    lo32, hi32 = _log_ratio32(ratio)
+    buf = torch.empty(1) if _scratch is None else _scratch
+    for _ in range(10):
+        target_area = area * buf.uniform_(scale[0], scale[1], generator=generator).item()
+        aspect = buf.uniform_(lo32, hi32, generator=generator).exp_().item()
+        w = int(round(math.sqrt(target_area * aspect)))
+        h = int(round(math.sqrt(target_area / aspect)))
+        if 0 < w <= width and 0 < h <= height:
+            top = torch.randint(0, height - h + 1, size=(1,), generator=generator).item()
+            left = torch.randint(0, width - w + 1, size=(1,), generator=generator).item()
+            return top, left, h, w
+    in_ratio = float(width) / float(height)
+    if in_ratio < min(ratio):
+        w = width
+        h = int(round(w / min(ratio)))
+    elif in_ratio > max(ratio):
+        h = height
+        w = int(round(h * max(ratio)))
+    else:
+        w, h = width, height
+    return (height - h) // 2, (width - w) // 2, h, w
+
+
+def draw_batch_params(n, height, width, generator=None, random_crop=True, flip_p=0.5):
+    """Per-sample (box, flip) for a batch; per sample the draws are get_params then
+    ``torch.rand(1) < p`` - the order a torchvision Compose([RandomResizedCrop, RandomHorizontalFlip])
+    consumes the generator in.  Returns (int32 [n,4], uint8 [n]) CPU tensors."""
+    if not random_crop:
+        return (torch.tensor([[0, 0, height, width]] * n, dtype=torch.int32), torch.zeros(n, dtype=torch.uint8))
+    rows, flips = [], []
+    buf = torch.empty(1)
+    for _ in range(n):
+        rows.append(rrc_params(height, width, generator=generator, _scratch=buf))
+        flips.append(1 if buf.uniform_(0.0, 1.0, generator=generator).item() < flip_p else 0)
+    return torch.tensor(rows, dtype=torch.int32), torch.tensor(flips, dtype=torch.uint8)
+
+
+class DeviceInputStage:
+    """uint8 NHWC host (pinned) or device batch -> normalised channels-last activation on the GPU."""
+
+    def __init__(self, out_size, mean, std, dtype=torch.bfloat16, device=None, layout=_cabi.LAYOUT_NHWC):
+        self.out_h, self.out_w = (out_size, out_size) if isinstance(out_size, int) else out_size
+        self.mean, self.std, self.dtype, self.layout = tuple(mean), tuple(std), dtype, layout
+        self.device = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+
+    def __call__(self, images_u8, boxes, flips):
+        dev = self.device
+        images_u8 = images_u8.to(dev, non_blocking=True)
+        boxes = boxes.to(dev, non_blocking=True)
+        flips = None if flips is None else flips.to(dev, non_blocking=True)
+        return _cabi.input_stage(images_u8, boxes, flips, self.out_h, self.out_w, self.mean, self.std, self.dtype,
+                                 self.layout)
+
+
+class SyntheticImageNet:
+    """Iterable of (input, target) like the reference's DataLoader (imagenet.py:350-354), over
+    synthetic uint8 images.  ``host=True`` keeps the batch in pinned host memory and copies it every
+    step (end-to-end path); ``host=False`` keeps it resident in HBM.  Images are seeded per rank
+    (``seed + rank``); one fixed image batch is re-used, the crop boxes / flips / targets are drawn per
+    step unless ``fixed_params``."""
+
+    def __init__(self, batch_size, steps, src_size=256, out_size=224, num_classes=1000, rank=0, seed=1234,
+                 random_crop=True, mean=IMAGENET_MEAN, std=IMAGENET_STD, dtype=torch.bfloat16, host=False,
+                 fixed_params=False, device=None):
+        self.batch_size, self.steps, self.num_classes = batch_size, steps, num_classes
+        self.src_h, self.src_w = (src_size, src_size) if isinstance(src_size, int) else src_size
+        self.random_crop, self.host, self.fixed_params = random_crop, host, fixed_params
+        self.gen = torch.Generator()
+        self.gen.manual_seed(seed + rank)
+        self.stage = DeviceInputStage(out_size, mean, std, dtype, device)
+        img = torch.randint(0, 256, (batch_size, self.src_h, self.src_w, 3), dtype=torch.uint8, generator=self.gen)
+        self.images = img.pin_memory() if host else img.to(self.stage.device)
+        self._fixed = None
+        self.h2d_bytes = 0
+
+    def __len__(self):
+        return self.steps
+
+    def _params(self):
+        if self.fixed_params and self._fixed is not None:
+            return self._fixed
+        boxes, flips = draw_batch_params(self.batch_size, self.src_h, self.src_w, self.gen, self.random_crop)
+        target = torch.randint(0, self.num_classes, (self.batch_size,), dtype=torch.int64, generator=self.gen)
+        out = (boxes.pin_memory(), flips.pin_memory(), target.pin_memory())
+        if self.fixed_params:
+            self._fixed = out
+        return out
+
+    def __iter__(self):
+        for _ in range(self.steps):
+            boxes, flips, target = self._params()
+            x = self.stage(self.images, boxes, flips)
+            self.h2d_bytes = (self.images.numel() if self.host else 0) + boxes.numel() * 4 + flips.numel() + \
+                target.numel() * 8
+            yield x, target.to(self.stage.device, non_blocking=True)

@@ -1,0 +1,92 @@
+"""Data-parallel wrapper over the flat gradient arena.
+
+Replaces ``DistributedDataParallel(model, device_ids=[local_rank], output_device=local_rank)``
+(imagenet.py:316) and the C++ Reducer behind it (reducer.hpp:347-524):
+
+* construction: parameters and BatchNorm buffers are broadcast from rank 0 (``_sync_module_states``,
+  torch/nn/parallel/distributed.py:883-890);
+* every training iteration the BatchNorm buffers of rank 0 overwrite everyone's before the next
+  forward (``_sync_buffers``, distributed.py:1590-1591,2214-2257).  Here that is ONE broadcast of the
+  contiguous buffer arena, issued right after the forward that updated the statistics so it overlaps
+  the backward, and waited for at the start of the next forward;
+* backward: gradients are written by the model straight into the flat arena (no bucket copy-in /
+  copy-out); as the backward passes each bucket boundary the slice is all-reduced (SUM) with NCCL on
+  its own stream while the rest of the backward keeps the GPU busy.  The 1/world_size pre-division
+  (reducer.hpp:497-500) is folded into the first backward op, so after ``loss.backward()`` ``p.grad``
+  holds the same averaged gradient the reference sees;
+* ``state_dict()`` keys carry the ``module.`` prefix exactly like the reference's checkpoint
+  (imagenet.py:392) and are detached clones in standard (contiguous) layout.
+"""
+import torch
+import torch.distributed as dist
+import torch.nn as nn
+
+
+class FlatDDP(nn.Module):
+    def __init__(self, module, device_ids=None, output_device=None, process_group=None, bucket_cap_mb=25,
+                 first_bucket_mb=1, broadcast_buffers=True):
+        super().__init__()
+        if not hasattr(module, "arena"):
+            raise TypeError("FlatDDP wraps a B200ResNet (flat parameter arena); got " + type(module).__name__)
+        self.module = module
+        self.process_group = process_group
+        self.world_size = dist.get_world_size(process_group) if dist.is_available() and dist.is_initialized() else 1
+        self.broadcast_buffers = broadcast_buffers
+        self._works = []
+        self._buffer_work = None
+        module.attach_sink(self)
+        module.grad_predivide = 1.0 / self.world_size
+        a = module.arena
+        # buckets: walk the backward's progress marks from the end of the arena, cut when a bucket
+        # reaches the cap (first = last layers' bucket is small so communication starts early)
+        marks = module.mark_offsets()  # descending, ends with 0
+        self.buckets = []
+        hi, cap = a.numel, first_bucket_mb * (1 << 20)
+        for m in marks:
+            if (hi - m) * 4 >= cap or m == 0:
+                if hi > m:
+                    self.buckets.append((m, hi))
+                    hi, cap = m, bucket_cap_mb * (1 << 20)
+        self._next = 0
+        if self.world_size > 1:
+            dist.broadcast(a.params, 0, group=process_group)
+            dist.broadcast(module.buffer_arena, 0, group=process_group)
+            a.refresh_shadow()
+
+    # ---- called by the model's backward ---------------------------------------------------------
+    def grad_ready(self, offset):
+        if self.world_size == 1:
+            return
+        g = self.module.arena.grads
+        while self._next < len(self.buckets) and self.buckets[self._next][0] >= offset:
+            lo, hi = self.buckets[self._next]
+            self._works.append(dist.all_reduce(g[lo:hi], op=dist.ReduceOp.SUM, group=self.process_group,
+                                               async_op=True))
+            self._next += 1
+
+    def backward_done(self):
+        for w in self._works:
+            w.wait()  # stream-level wait: the optimizer's kernels queue behind the all-reduces
+        self._works = []
+        self._next = 0
+
+    # ---- nn.Module surface ----------------------------------------------------------------------
+    def forward(self, *args, **kwargs):
+        if self._buffer_work is not None:
+            self._buffer_work.wait()
+            self._buffer_work = None
+        out = self.module(*args, **kwargs)
+        if (self.world_size > 1 and self.broadcast_buffers and self.module.training and torch.is_grad_enabled()):
+            self._buffer_work = dist.broadcast(self.module.buffer_arena, 0, group=self.process_group, async_op=True)
+        return out
+
+    def state_dict(self, *args, **kwargs):
+        if self._buffer_work is not None:
+            self._buffer_work.wait()
+            self._buffer_work = None
+        sd = super().state_dict(*args, **kwargs)
+        return type(sd)((k, v.detach().clone(memory_format=torch.contiguous_format)) for k, v in sd.items())
+
+
+# the name the reference imports (imagenet.py:28)
+DistributedDataParallel = FlatDDP

@@ -1,0 +1,179 @@
+"""Command-line trainer with the reference's flags, outputs and epoch loop (imagenet.py:213-452).
+
+    srun python -m imagent_distributed_training_pytorch_with_slurm_b200.imagenet --backend=nccl        # Slurm
+    python -m torch.distributed.run --nproc-per-node 8 -m ...imagenet --synthetic 40960 --arch resnet50  # one box
+
+Kept byte for byte: the six flags and their defaults (imagenet.py:437-449), the rank summary
+(:252-262), SGD hyper-parameters (:325), LR schedule (:154-162), the epoch summary lines (:398-403),
+the TensorBoard directory / tags / step offsets (:363,405-421: ``lr`` is logged at ``epoch``, the rest
+at ``epoch+1``), the best-epoch bookkeeping and the ``module.``-prefixed float32 checkpoint
+``imagenet_FR_resnet18.pt`` (:388-392; ``imagenet_FR_<arch>.pt`` for other archs).
+
+Added flags default to the reference's behaviour where it has one: ``--arch resnet18``,
+``--image-size 448``.  ``--synthetic N`` (images per epoch) selects seeded synthetic uint8 data; the
+on-disk ``datasets.ImageNet`` front end (imagenet.py:287-296) is outside this package's scope.
+Rendezvous: the reference's SLURM variables (:225-244) when present, else torchrun's
+``RANK/LOCAL_RANK/WORLD_SIZE``, else a single process.
+"""
+import argparse
+import os
+import socket
+import subprocess
+
+import torch
+import torch.distributed as dist
+
+from . import data as b200_data
+from .ddp import FlatDDP
+from .engine import adjust_learning_rate, train, validate
+from .loss import CrossEntropyLoss
+from .optim import FlatSGD
+from .resnet import build_model
+
+
+def _rendezvous():
+    env = os.environ
+    if "SLURM_PROCID" in env and "SLURM_NTASKS" in env:
+        n_nodes = int(env["SLURM_JOB_NUM_NODES"])
+        node_id = int(env["SLURM_NODEID"])
+        local_rank = int(env["SLURM_LOCALID"])
+        global_rank = int(env["SLURM_PROCID"])
+        world_size = int(env["SLURM_NTASKS"])
+        hostnames = subprocess.check_output(["scontrol", "show", "hostnames", env["SLURM_JOB_NODELIST"]])
+        env["MASTER_ADDR"] = hostnames.split()[0].decode("utf-8")
+        env["MASTER_PORT"] = str(29500)
+    else:
+        n_nodes, node_id = int(env.get("GROUP_WORLD_SIZE", 1)), int(env.get("GROUP_RANK", 0))
+        local_rank = int(env.get("LOCAL_RANK", 0))
+        global_rank = int(env.get("RANK", 0))
+        world_size = int(env.get("WORLD_SIZE", 1))
+        env.setdefault("MASTER_ADDR", "127.0.0.1")
+        env.setdefault("MASTER_PORT", str(29500))
+    env["WORLD_SIZE"] = str(world_size)
+    env["RANK"] = str(global_rank)
+    return n_nodes, node_id, local_rank, global_rank, world_size
+
+
+def run(args):
+    torch.manual_seed(args.seed)
+    n_nodes, node_id, local_rank, global_rank, world_size = _rendezvous()
+    n_gpu_per_node = world_size // n_nodes
+    is_master = node_id == 0 and local_rank == 0
+
+    prefix = "%i - " % global_rank
+    print(prefix + "Number of nodes: %i" % n_nodes)
+    print(prefix + "Node ID        : %i" % node_id)
+    print(prefix + "Local rank     : %i" % local_rank)
+    print(prefix + "Global rank    : %i" % global_rank)
+    print(prefix + "World size     : %i" % world_size)
+    print(prefix + "GPUs per node  : %i" % n_gpu_per_node)
+    print(prefix + "Master         : %s" % str(is_master))
+    print(prefix + "Multi-node     : %s" % str(n_nodes > 1))
+    print(prefix + "Multi-GPU      : %s" % str(world_size > 1))
+    print(prefix + "Hostname       : %s" % socket.gethostname())
+
+    torch.cuda.set_device(local_rank)
+    torch.backends.cudnn.benchmark = True
+    print("Initializing PyTorch distributed ...")
+    dist.init_process_group(init_method="env://", backend=args.backend)
+    print(f"Backend: {dist.get_backend()}")
+
+    print("Initialize Dataloaders...")
+    if not args.synthetic:
+        raise NotImplementedError(
+            "the datasets.ImageNet on-disk front end (imagenet.py:287-296) is not part of this package; "
+            "pass --synthetic <images per epoch>")
+    num_classes = 1000
+    ref_mode = not args.random_crop
+    mean, std = (b200_data.REFERENCE_MEAN, b200_data.REFERENCE_STD) if ref_mode else \
+        (b200_data.IMAGENET_MEAN, b200_data.IMAGENET_STD)
+    dtype = torch.float32 if args.fp32 else torch.bfloat16
+    per_rank = -(-args.synthetic // world_size)
+    steps = -(-per_rank // args.batch_size)
+    val_steps = max(1, steps // 25)
+    common = dict(src_size=args.source_size, out_size=args.image_size, num_classes=num_classes, rank=global_rank,
+                  mean=mean, std=std, dtype=dtype, host=True)
+    train_loader = b200_data.SyntheticImageNet(args.batch_size, steps, random_crop=not ref_mode, **common)
+    val_loader = b200_data.SyntheticImageNet(args.batch_size, val_steps, random_crop=False, seed=4321, **common)
+    print("Training samples: {} images ".format(steps * args.batch_size * world_size))
+    print("Test samples: {} images ".format(val_steps * args.batch_size * world_size))
+    print("number of classes: {}".format(num_classes))
+
+    print("Initialize Model...")
+    model = build_model(args.arch, num_classes=num_classes, dtype=dtype).cuda()
+    model = FlatDDP(model, device_ids=[local_rank], output_device=local_rank)
+    criterion = CrossEntropyLoss().cuda()
+    optimizer = FlatSGD(model.parameters(), args.lr, momentum=0.9, weight_decay=1e-4)
+
+    writer = None
+    if is_master:
+        from torch.utils.tensorboard import SummaryWriter
+
+        writer = SummaryWriter("imagenet_FR")
+
+    best_top5 = best_top1 = 0
+    total_time = 0
+    best_epoch_top1 = best_epoch_top5 = 0
+    ckpt = "imagenet_FR_resnet18.pt" if args.arch == "resnet18" else f"imagenet_FR_{args.arch}.pt"
+    for epoch in range(args.epochs):
+        lr = adjust_learning_rate(args.lr, optimizer, epoch)
+        train_loss, train_prec1, train_prec5, epoch_t1 = train(train_loader, model, criterion, optimizer, epoch,
+                                                               world_size)
+        val_loss, val_prec1, val_prec5, epoch_t2 = validate(val_loader, model, criterion, world_size)
+        total_time += epoch_t1 + epoch_t2
+        if val_prec1 > best_top1:
+            best_top1, best_epoch_top1 = val_prec1, epoch
+            if is_master and args.save_model:
+                torch.save(model.state_dict(), ckpt)
+        if val_prec5 > best_top5:
+            best_top5, best_epoch_top5 = val_prec5, epoch
+        if is_master:
+            print(f"Epoch {epoch+1} Summary: ")
+            print(f"\tLearning rate: {lr}")
+            print(f"\tTrain loss: {train_loss} ; Test loss: {val_loss}")
+            print(f"\tTrain top1 accuracy: {train_prec1} ; Test top1 accuracy: {val_prec1}")
+            print(f"\tTrain top5 accuracy: {train_prec5} ; Test top5 accuracy: {val_prec5}")
+            print(f"\tTrain time: {epoch_t1} seconds; Test time:{epoch_t2} seconds")
+            writer.add_scalars("Loss", {"train": train_loss, "val": val_loss}, epoch + 1)
+            writer.add_scalars("Top1 accuracy", {"train": train_prec1, "val": val_prec1}, epoch + 1)
+            writer.add_scalars("Top5 accuracy", {"train": train_prec5, "val": val_prec5}, epoch + 1)
+            writer.add_scalar("lr", lr, epoch)
+    if is_master:
+        print("\n")
+        print("Training Summary:")
+        print(f"\tTop1 best epoch: {best_epoch_top1}")
+        print(f"\t Best Test top1 accuracy: {best_top1}")
+        print(f"\tTop5 best epoch: {best_epoch_top5}")
+        print(f"\t Best Test top5 accuracy: {best_top5}")
+        print(f"\tTraining time: {total_time/60} minutes")
+        writer.close()
+    dist.destroy_process_group()
+
+
+def build_parser():
+    parser = argparse.ArgumentParser(description="Imagenet Pytorch")
+    # the reference's flags (imagenet.py:437-449), defaults unchanged
+    parser.add_argument("--seed", default=0, type=int, help="seed for initializing training. ")
+    parser.add_argument("--backend", type=str, default="nccl")
+    parser.add_argument("--batch-size", type=int, default=128, metavar="N", help="input batch size per GPU")
+    parser.add_argument("--epochs", type=int, default=100, metavar="N", help="number of epochs to train")
+    parser.add_argument("--lr", type=float, default=0.1, metavar="LR", help="learning rate (default: .1)")
+    parser.add_argument("--save-model", action="store_true", default=False, help="For Saving the current Model")
+    # additions
+    parser.add_argument("--arch", type=str, default="resnet18", help="torchvision ResNet constructor name")
+    parser.add_argument("--image-size", type=int, default=448, help="network input size (reference: 448)")
+    parser.add_argument("--source-size", type=int, default=500, help="synthetic source image size")
+    parser.add_argument("--synthetic", type=int, default=0, metavar="IMAGES", help="synthetic images per epoch")
+    parser.add_argument("--random-crop", action="store_true", default=False,
+                        help="RandomResizedCrop + horizontal flip + ImageNet mean/std instead of the reference's "
+                             "plain resize and 0.5/0.5 normalisation")
+    parser.add_argument("--fp32", action="store_true", default=False, help="float32 activations instead of bf16")
+    return parser
+
+
+def main(argv=None):
+    run(build_parser().parse_args(argv))
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,387 @@
+"""torchvision-compatible ResNets executed as one hand-scheduled forward/backward.
+
+Replaces ``models.resnet18(pretrained=False, num_classes=...)`` (imagenet.py:312) and what
+``loss.backward()`` (imagenet.py:128) does to it.  Same constructor RNG consumption, same
+``state_dict`` keys / shapes / dtypes as the torchvision module (resnet.py:166-285), but:
+
+* parameters, their gradients and the momentum buffers live in ONE flat float32 arena each
+  (``ParamArena``); the ``nn.Parameter`` objects are views into it, ``p.grad`` is a permanent view of
+  the gradient arena.  Convolution weights are stored KRSC (channels-last) so cuDNN needs no
+  per-call transposes; a bf16 shadow arena with the same layout feeds the bf16 convolutions and is
+  refreshed by the fused SGD kernel;
+* the network is a single autograd node: the forward records a tape, the backward walks it in
+  reverse calling cuDNN (dgrad/wgrad), the B200 BatchNorm(+add)+ReLU kernels and cuBLAS directly,
+  writing every parameter gradient straight into the gradient arena and telling the data-parallel
+  wrapper how far it has got so bucket all-reduces overlap the rest of the backward;
+* activations are channels-last, bf16 (default) or float32.
+
+BatchNorm sites: ``bn+relu`` resnet.py:93-94,147-152,269-270; ``bn+add+relu`` :97-103,155-161;
+``bn`` (downsample) :240-243.  Convolutions and the final Linear stay on cuDNN / cuBLAS.
+"""
+import math
+
+import torch
+import torch.nn as nn
+
+from . import _cabi
+
+_ALIGN = 32  # floats: every parameter starts on a 128-byte boundary of the arena
+
+
+class ParamArena:
+    """Flat storage for parameters / gradients / momentum (float32) and the bf16 shadow."""
+
+    def __init__(self, shapes, device, shadow):
+        self.offsets = []
+        off = 0
+        for shp in shapes:
+            self.offsets.append(off)
+            n = int(math.prod(shp))
+            off += (n + _ALIGN - 1) // _ALIGN * _ALIGN
+        self.numel = off
+        self.shapes = list(shapes)
+        self.device = device
+        self.params = torch.zeros(off, dtype=torch.float32, device=device)
+        self.grads = torch.zeros(off, dtype=torch.float32, device=device)
+        self.momentum = torch.zeros(off, dtype=torch.float32, device=device)
+        self.shadow = torch.zeros(off, dtype=torch.bfloat16, device=device) if shadow else None
+        self.steps = 0
+
+    def view(self, flat, i):
+        shp = self.shapes[i]
+        seg = flat[self.offsets[i]: self.offsets[i] + int(math.prod(shp))]
+        if len(shp) == 4:  # [K,C,R,S] stored as K,R,S,C
+            k, c, r, s = shp
+            return seg.view(k, r, s, c).permute(0, 3, 1, 2)
+        return seg.view(*shp)
+
+    def refresh_shadow(self):
+        if self.shadow is not None:
+            self.shadow.copy_(self.params)
+
+
+class _Conv(nn.Module):
+    def __init__(self, tv):
+        super().__init__()
+        self.stride, self.padding, self.dilation, self.groups = tv.stride, tv.padding, tv.dilation, tv.groups
+        self.weight = None  # set by _adopt
+        self.w_compute = None
+        self.grad_view = None
+
+    def fwd(self, x):
+        return torch.ops.aten.convolution(x, self.w_compute, None, self.stride, self.padding, self.dilation, False,
+                                          (0, 0), self.groups)
+
+    def bwd(self, gy, x, need_gx=True):
+        gx, gw, _ = torch.ops.aten.convolution_backward(gy, x, self.w_compute, None, self.stride, self.padding,
+                                                        self.dilation, False, (0, 0), self.groups,
+                                                        (need_gx, True, False))
+        self.grad_view.copy_(gw)
+        return gx
+
+
+class _BN(nn.Module):
+    def __init__(self, tv):
+        super().__init__()
+        self.eps, self.momentum, self.num_features = tv.eps, tv.momentum, tv.num_features
+        self.weight = None
+        self.bias = None
+        self.g_weight = None
+        self.g_bias = None
+
+    def fwd_train(self, x, act, z=None):
+        return _cabi.bn_fwd_train(x, z, self.weight, self.bias, self.running_mean, self.running_var,
+                                  self.num_batches_tracked, self.eps, self.momentum, act)
+
+    def fwd_eval(self, x, act, z=None):
+        return _cabi.bn_fwd_eval(x, z, self.weight, self.bias, self.running_mean, self.running_var, self.eps, act)
+
+    def bwd(self, dy, x, saved, mask, act):
+        dx, dz, _, _ = _cabi.bn_bwd(dy, x, mask, self.weight, saved, act, self.g_weight, self.g_bias)
+        return dx, dz
+
+
+class _Linear(nn.Module):
+    def __init__(self, tv):
+        super().__init__()
+        self.in_features, self.out_features = tv.in_features, tv.out_features
+        self.weight = None
+        self.bias = None
+
+
+class _Block(nn.Module):
+    """BasicBlock (resnet.py:59-105) or Bottleneck (resnet.py:108-163)."""
+
+    def __init__(self, tv):
+        super().__init__()
+        self.n_conv = 3 if hasattr(tv, "conv3") else 2
+        for i in range(1, self.n_conv + 1):
+            setattr(self, f"conv{i}", _Conv(getattr(tv, f"conv{i}")))
+            setattr(self, f"bn{i}", _BN(getattr(tv, f"bn{i}")))
+        if tv.downsample is not None:
+            self.downsample = nn.Sequential(_Conv(tv.downsample[0]), _BN(tv.downsample[1]))
+        else:
+            self.downsample = None
+
+    def convs(self):
+        return [(getattr(self, f"conv{i}"), getattr(self, f"bn{i}")) for i in range(1, self.n_conv + 1)]
+
+    def fwd_train(self, x):
+        tape = {"in": x, "x": [], "a": [], "saved": []}
+        cur = x
+        pairs = self.convs()
+        for conv, bn in pairs[:-1]:
+            t = conv.fwd(cur)
+            cur, saved, _ = bn.fwd_train(t, _cabi.ACT_RELU)
+            tape["x"].append(t)
+            tape["a"].append(cur)
+            tape["saved"].append(saved)
+        conv, bn = pairs[-1]
+        t = conv.fwd(cur)
+        if self.downsample is not None:
+            td = self.downsample[0].fwd(x)
+            zd, saved_d, _ = self.downsample[1].fwd_train(td, _cabi.ACT_NONE)
+            tape["td"], tape["saved_d"] = td, saved_d
+        else:
+            zd = x
+        out, saved, mask = bn.fwd_train(t, _cabi.ACT_ADD_RELU, zd)
+        tape["x"].append(t)
+        tape["saved"].append(saved)
+        tape["mask"] = mask
+        return out, tape
+
+    def fwd_eval(self, x):
+        cur = x
+        pairs = self.convs()
+        for conv, bn in pairs[:-1]:
+            cur = bn.fwd_eval(conv.fwd(cur), _cabi.ACT_RELU)
+        conv, bn = pairs[-1]
+        t = conv.fwd(cur)
+        zd = x if self.downsample is None else self.downsample[1].fwd_eval(self.downsample[0].fwd(x), _cabi.ACT_NONE)
+        return bn.fwd_eval(t, _cabi.ACT_ADD_RELU, zd)
+
+    def bwd(self, g_out, tape, need_gx=True):
+        pairs = self.convs()
+        conv, bn = pairs[-1]
+        g, g_z = bn.bwd(g_out, tape["x"].pop(), tape["saved"].pop(), tape.pop("mask"), _cabi.ACT_ADD_RELU)
+        del g_out
+        for conv_prev, bn_prev in reversed(pairs[:-1]):
+            g = conv.bwd(g, tape["a"].pop())
+            g, _ = bn_prev.bwd(g, tape["x"].pop(), tape["saved"].pop(), None, _cabi.ACT_RELU)
+            conv = conv_prev
+        x_in = tape.pop("in")
+        g = conv.bwd(g, x_in, need_gx)
+        if self.downsample is not None:
+            g_td, _ = self.downsample[1].bwd(g_z, tape.pop("td"), tape.pop("saved_d"), None, _cabi.ACT_NONE)
+            del g_z
+            g2 = self.downsample[0].bwd(g_td, x_in, need_gx)
+        else:
+            g2 = g_z
+        if need_gx:
+            g.add_(g2)
+        return g
+
+
+class _WholeNet(torch.autograd.Function):
+    """The network as one autograd node (so ``loss.backward()`` drives our own backward pass)."""
+
+    @staticmethod
+    def forward(ctx, x, anchor, net):
+        logits, tape = net._forward_train(x)
+        ctx.net, ctx.tape = net, tape
+        return logits
+
+    @staticmethod
+    @torch.autograd.function.once_differentiable
+    def backward(ctx, g_logits):
+        net, tape = ctx.net, ctx.tape
+        ctx.tape = None
+        net._backward(tape, g_logits)
+        return None, None, None
+
+
+class B200ResNet(nn.Module):
+    """Drop-in for a torchvision ResNet (``models.<arch>(weights=None, num_classes=...)``)."""
+
+    def __init__(self, arch="resnet18", num_classes=1000, device=None, dtype=torch.bfloat16):
+        super().__init__()
+        import torchvision.models as tvm
+
+        if dtype not in (torch.bfloat16, torch.float32):
+            raise ValueError("activation dtype must be torch.bfloat16 or torch.float32")
+        ctor = getattr(tvm, arch, None)
+        if ctor is None:
+            raise ValueError(f"unknown torchvision arch {arch!r}")
+        tv = ctor(weights=None, num_classes=num_classes)  # same RNG draws as the reference's constructor
+        if not isinstance(tv, tvm.ResNet):
+            raise ValueError(f"{arch!r} is not a torchvision ResNet; only that family is implemented")
+        if device is None:
+            device = torch.device("cuda", torch.cuda.current_device())
+        device = torch.device(device)  # kernels raise on non-CUDA tensors: there is no CPU path
+        self.arch, self.act_dtype, self.device = arch, dtype, device
+
+        self.conv1, self.bn1 = _Conv(tv.conv1), _BN(tv.bn1)
+        self.pool = (tv.maxpool.kernel_size, tv.maxpool.stride, tv.maxpool.padding)
+        for li in range(1, 5):
+            setattr(self, f"layer{li}", nn.Sequential(*[_Block(b) for b in getattr(tv, f"layer{li}")]))
+        self.fc = _Linear(tv.fc)
+        self._adopt(tv)
+        self._anchor = torch.zeros((), device=device, requires_grad=True)
+        self.__dict__["_sink"] = None  # data-parallel wrapper (grad_ready / backward_done); not a submodule
+        self.grad_predivide = 1.0  # 1/world_size, set by the wrapper (DDP's pre-division)
+
+    # ---- storage --------------------------------------------------------------------------------
+    def _adopt(self, tv):
+        """Move the torchvision module's parameters/buffers into flat arenas, keeping key order."""
+        tv_params = dict(tv.named_parameters())
+        tv_mods = dict(tv.named_modules())
+        names = [n for n, _ in tv.named_parameters()]
+        self.arena = ParamArena([tuple(tv_params[n].shape) for n in names], self.device,
+                                shadow=self.act_dtype == torch.bfloat16)
+        a = self.arena
+        self.param_names = names
+        self.param_index = {n: i for i, n in enumerate(names)}
+        bn_mods = [n for n, m in tv.named_modules() if isinstance(m, nn.BatchNorm2d)]
+        nfeat = sum(tv_mods[n].num_features for n in bn_mods)
+        # buffer arena: [running_mean/var float32 ... | num_batches_tracked int64 ...] in one byte buffer
+        fbytes = 4 * 2 * nfeat
+        fbytes = (fbytes + 15) // 16 * 16
+        self.buffer_arena = torch.zeros(fbytes + 8 * len(bn_mods), dtype=torch.uint8, device=self.device)
+        fview = self.buffer_arena[:4 * 2 * nfeat].view(torch.float32)
+        iview = self.buffer_arena[fbytes:].view(torch.int64)
+        own = dict(self.named_modules())
+        boff = 0
+        for bi, n in enumerate(bn_mods):
+            m, src = own[n], tv_mods[n]
+            c = src.num_features
+            m.register_buffer("running_mean", fview[boff:boff + c])
+            m.register_buffer("running_var", fview[boff + c:boff + 2 * c])
+            m.register_buffer("num_batches_tracked", iview[bi])
+            m.running_mean.copy_(src.running_mean)
+            m.running_var.copy_(src.running_var)
+            boff += 2 * c
+        with torch.no_grad():
+            for i, n in enumerate(names):
+                modname, leaf = n.rsplit(".", 1)
+                m = own[modname]
+                pv = a.view(a.params, i)
+                pv.copy_(tv_params[n])
+                p = nn.Parameter(pv)
+                p._b200_arena, p._b200_index = a, i
+                p.grad = a.view(a.grads, i)
+                setattr(m, leaf, p)
+                if isinstance(m, _Conv):
+                    m.grad_view = a.view(a.grads, i)
+                    m.w_compute = a.view(a.shadow, i) if a.shadow is not None else p.detach()
+                elif isinstance(m, _BN):
+                    if leaf == "weight":
+                        m.g_weight = a.view(a.grads, i)
+                    else:
+                        m.g_bias = a.view(a.grads, i)
+                elif isinstance(m, _Linear):
+                    src = a.shadow if a.shadow is not None else a.params
+                    setattr(m, "w_compute" if leaf == "weight" else "b_compute", a.view(src, i))
+                    setattr(m, "g_" + leaf, a.view(a.grads, i))
+        a.refresh_shadow()
+        # arena offsets at which the backward reports progress (start of each block, then the stem)
+        self._marks = {}
+        for li in range(1, 5):
+            for bi, _ in enumerate(getattr(self, f"layer{li}")):
+                self._marks[(li, bi)] = a.offsets[self.param_index[f"layer{li}.{bi}.conv1.weight"]]
+        self._marks["fc"] = a.offsets[self.param_index["fc.weight"]]
+
+    def mark_offsets(self):
+        """Arena offsets (descending) at which gradients become final during the backward."""
+        return sorted(set(self._marks.values()) | {0}, reverse=True)
+
+    def attach_sink(self, sink):
+        self.__dict__["_sink"] = sink  # bypass nn.Module registration (the wrapper owns us, not vice versa)
+
+    # ---- execution ------------------------------------------------------------------------------
+    def _prep_input(self, x):
+        if x.device != self.device:
+            raise _cabi.B200Error("input must already be on the model's CUDA device")
+        if x.dtype != self.act_dtype or not x.is_contiguous(memory_format=torch.channels_last):
+            x = x.to(dtype=self.act_dtype, memory_format=torch.channels_last)
+        return x
+
+    def forward(self, x):
+        x = self._prep_input(x)
+        if self.training and torch.is_grad_enabled():
+            return _WholeNet.apply(x, self._anchor, self)
+        if self.training:
+            return self._forward_train(x)[0]
+        return self._forward_eval(x)
+
+    def _forward_train(self, x):
+        tape = {"x0": x}
+        t = self.conv1.fwd(x)
+        a, saved, _ = self.bn1.fwd_train(t, _cabi.ACT_RELU)
+        tape["t1"], tape["saved1"], tape["a1"] = t, saved, a
+        k, s, p = self.pool
+        cur, idx = torch.ops.aten.max_pool2d_with_indices(a, [k, k], [s, s], [p, p], [1, 1], False)
+        tape["pool_idx"] = idx
+        tape["blocks"] = []
+        for li in range(1, 5):
+            for blk in getattr(self, f"layer{li}"):
+                cur, bt = blk.fwd_train(cur)
+                tape["blocks"].append(bt)
+        tape["last_shape"] = cur.shape
+        feat = cur.mean((2, 3))
+        tape["feat"] = feat
+        logits = torch.addmm(self.fc.b_compute, feat, self.fc.w_compute.t())
+        return logits, tape
+
+    def _forward_eval(self, x):
+        a = self.bn1.fwd_eval(self.conv1.fwd(x), _cabi.ACT_RELU)
+        k, s, p = self.pool
+        cur = torch.ops.aten.max_pool2d(a, [k, k], [s, s], [p, p], [1, 1], False)
+        for li in range(1, 5):
+            for blk in getattr(self, f"layer{li}"):
+                cur = blk.fwd_eval(cur)
+        feat = cur.mean((2, 3))
+        return torch.addmm(self.fc.b_compute, feat, self.fc.w_compute.t())
+
+    def _backward(self, tape, g_logits):
+        sink = self._sink
+        fc = self.fc
+        g_logits = g_logits.contiguous()
+        pre = self.grad_predivide
+        feat = tape.pop("feat")
+        # Linear backward on cuBLAS; DDP's 1/world pre-division rides on alpha
+        g_feat = torch.addmm(feat, g_logits, fc.w_compute, beta=0.0, alpha=pre)
+        if g_logits.dtype == torch.float32:
+            torch.addmm(fc.g_weight, g_logits.t(), feat, beta=0.0, alpha=pre, out=fc.g_weight)
+            torch.sum(g_logits, 0, out=fc.g_bias)
+            if pre != 1.0:
+                fc.g_bias.mul_(pre)
+        else:
+            fc.g_weight.copy_(torch.addmm(fc.w_compute, g_logits.t(), feat, beta=0.0, alpha=pre))
+            fc.g_bias.copy_(g_logits.sum(0, dtype=torch.float32) * pre)
+        if sink is not None:
+            sink.grad_ready(self._marks["fc"])
+        n, c, h, w = tape.pop("last_shape")
+        g = (g_feat * (1.0 / (h * w))).view(n, c, 1, 1).expand(n, c, h, w).contiguous(memory_format=torch.channels_last)
+        blocks = tape.pop("blocks")
+        for li in range(4, 0, -1):
+            layer = getattr(self, f"layer{li}")
+            for bi in range(len(layer) - 1, -1, -1):
+                g = layer[bi].bwd(g, blocks.pop())
+                if sink is not None:
+                    sink.grad_ready(self._marks[(li, bi)])
+        k, s, p = self.pool
+        a1 = tape.pop("a1")
+        g = torch.ops.aten.max_pool2d_with_indices_backward(g, a1, [k, k], [s, s], [p, p], [1, 1], False,
+                                                            tape.pop("pool_idx"))
+        del a1
+        g, _ = self.bn1.bwd(g, tape.pop("t1"), tape.pop("saved1"), None, _cabi.ACT_RELU)
+        self.conv1.bwd(g, tape.pop("x0"), need_gx=False)
+        if sink is not None:
+            sink.grad_ready(0)
+            sink.backward_done()
+
+
+def build_model(arch="resnet18", num_classes=1000, device=None, dtype=torch.bfloat16):
+    """``models.resnet18(pretrained=False, num_classes=num_classes).cuda()`` (imagenet.py:312) with
+    ``arch`` generalised; call after ``torch.manual_seed`` like the reference does."""
+    return B200ResNet(arch, num_classes, device, dtype)

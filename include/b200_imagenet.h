@@ -1,0 +1,157 @@
+/*
+ * b200_imagenet.h - C ABI of the B200 (sm_100a) kernels behind the data-parallel training step of
+ * the reference's imagenet.py (train(), imagenet.py:97-151).
+ *
+ * The reference is a pure PyTorch script with no FFI of its own; each entry point below names the
+ * reference call site (and the PyTorch dispatch behind it) that it replaces.  Conventions, the same
+ * for every function unless its comment says otherwise:
+ *   - plain pointers and sizes only; all data pointers are DEVICE pointers on the current device;
+ *   - returns 0 on success, otherwise a cudaError_t value (argument errors are reported as
+ *     cudaErrorInvalidValue = 1, misaligned pointers as cudaErrorMisalignedAddress = 716);
+ *     b200_error_string() turns the code into text;
+ *   - launches on the stream handed in (a cudaStream_t passed as void*; NULL = legacy default
+ *     stream), never synchronises the device, never allocates or frees device memory: scratch
+ *     ("workspace") is passed in by the caller and sized with the matching *_workspace_bytes();
+ *   - data pointers must be 16-byte aligned;
+ *   - dtype: B200_F32 (float) or B200_BF16 (__nv_bfloat16) for activations; statistics, parameters,
+ *     gradients of parameters and all accumulation are float32;
+ *   - activations are "rows x channels": a channels-last [N,H,W,C] tensor seen as [M = N*H*W, C].
+ */
+#ifndef B200_IMAGENET_H_
+#define B200_IMAGENET_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B200_ABI_VERSION 1
+
+enum { B200_F32 = 0, B200_BF16 = 1 };
+enum { B200_ACT_NONE = 0, B200_ACT_RELU = 1, B200_ACT_ADD_RELU = 2 };
+enum { B200_LAYOUT_NHWC = 0, B200_LAYOUT_NCHW = 1 };
+
+/* Library identity / diagnostics. */
+int b200_abi_version(void);
+const char *b200_error_string(int code);
+
+/* Process-wide launch tuning (no reference counterpart; used by the benchmark sweeps).  Keys:
+ *   "bn_target_ctas"   CTAs a BatchNorm pass aims for (default 148*8)
+ *   "bn_vec_bf16"      channels per thread for bf16 activations, 4 or 8 (default 8); forward and
+ *                      backward of one layer must run under the same value (it fixes the mask layout)
+ *   "bn_stats_reverse" 1 = statistics/reduce passes walk the rows back to front (default 1)
+ *   "bn_apply_reverse" 1 = apply passes walk the rows back to front (default 0)
+ * Returns cudaErrorInvalidValue for an unknown key or value. */
+int b200_tune_set(const char *key, int value);
+
+/* ------------------------------------------------------------------------------------------------
+ * K4b  fused flat-buffer SGD.
+ * Replaces optimizer.step() (imagenet.py:131; SGD built at imagenet.py:325 with momentum 0.9,
+ * weight_decay 1e-4, dampening 0, nesterov False), i.e. the four _foreach passes of
+ * torch/optim/sgd.py:425-473 whose per-element meaning is torch/optim/sgd.py:343-380:
+ *     g' = g*grad_scale + weight_decay*p ;  buf = first_step ? g' : momentum*buf + g' ;
+ *     p  = p - lr*buf
+ * over n contiguous float32 elements in ONE pass (read p,g,buf; write p,buf = 20 B/element).
+ * shadow_bf16, when not NULL, receives the updated p rounded to bfloat16 (the copy the bf16
+ * convolutions read), +2 B/element.  grad_scale folds DDP's 1/world_size
+ * (reducer.hpp:497-500) when the caller all-reduces un-divided sums; pass 1.0f otherwise.
+ */
+int b200_sgd_flat_f32(float *p, const float *g, float *buf, void *shadow_bf16, int64_t n, float lr,
+                      float weight_decay, float momentum, float grad_scale, int first_step, void *stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * K3  cross-entropy + top-1/top-5 in one kernel.
+ * Replaces criterion(logits, target) (imagenet.py:124; nn.CrossEntropyLoss() defaults,
+ * torch/nn/functional.py:3421-3504 = log_softmax + nll_loss mean) AND accuracy(logits, target,
+ * (1,5)) (imagenet.py:63-79,134 = topk + eq + sum).  One warp per row:
+ *     out3[0] = mean_n(logsumexp(x_n) - x_n[t_n])
+ *     out3[1] = 100/N * #{n : rank_n < 1},  out3[2] = 100/N * #{n : rank_n < 5}
+ * rank_n = #{j : x_nj > x_nt  or (x_nj == x_nt and j < t)}   (ties go to the lower class index).
+ * row_lse[n] = logsumexp(x_n) is kept for the backward.  Rows are summed in a fixed order by the
+ * last block to finish, so the result is bit-reproducible.  workspace must be zero-filled before
+ * its FIRST use (the kernel leaves it ready for the next call); calls sharing a workspace must not
+ * overlap on the GPU.  target values must lie in [0, c).
+ */
+size_t b200_ce_topk_workspace_bytes(int64_t n);
+int b200_ce_topk_fwd(const void *logits, const int64_t *target, float *out3, float *row_lse, void *workspace,
+                     size_t workspace_bytes, int64_t n, int64_t c, int dtype, void *stream);
+
+/* Backward of the loss above (loss.backward(), imagenet.py:128, first node):
+ *     dlogits[n][j] = (exp(x_nj - row_lse[n]) - [j == t_n]) * scale * (grad_out ? *grad_out : 1) / N
+ * grad_out is a DEVICE scalar (the upstream gradient, 1.0 for loss.backward()) or NULL; scale is a
+ * host-side multiplier.  dlogits has the dtype of logits.
+ */
+int b200_ce_bwd(const void *logits, const int64_t *target, const float *row_lse, const float *grad_out,
+                float scale, void *dlogits, int64_t n, int64_t c, int dtype, void *stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * K2  BatchNorm2d (+ residual add) + ReLU on channels-last rows.
+ * Replaces nn.BatchNorm2d in training mode followed by ReLU(inplace) and, in the residual blocks,
+ * `out += identity; out = relu(out)`:
+ *   B200_ACT_RELU     torchvision resnet.py:93-94,147-148,151-152,269-270
+ *   B200_ACT_ADD_RELU torchvision resnet.py:97-103,155-161           (y = relu(bn(x) + z))
+ *   B200_ACT_NONE     torchvision resnet.py:240-243 (downsample)
+ * arithmetic of torch/nn/modules/batchnorm.py:160-206: biased batch variance for the
+ * normalisation, running_var updated with the unbiased one, num_batches_tracked += 1.
+ *
+ * forward, training:  three launches (per-chunk shifted sums -> per-channel finalize -> apply).
+ *   saved: float[4*C] out = {mean, invstd, scale = gamma*invstd, shift = beta - mean*scale}
+ *   mask : B200_ACT_ADD_RELU only, out, M*C/vec bytes (one byte per `vec` channels, bit k set iff
+ *          the pre-activation of channel k of the group is > 0); vec = b200_bn_vec(dtype)
+ *   z    : B200_ACT_ADD_RELU only.  x,z,y: [M,C] of `dtype`.  Requires M >= 2, C % vec == 0.
+ */
+int b200_bn_vec(int dtype);
+size_t b200_bn_workspace_bytes(int64_t m, int c, int dtype);
+int b200_bn_fwd_train(const void *x, const void *z, void *y, uint8_t *mask, const float *gamma, const float *beta,
+                      float *running_mean, float *running_var, int64_t *num_batches_tracked, float *saved,
+                      void *workspace, size_t workspace_bytes, int64_t m, int c, float eps, float momentum, int act,
+                      int dtype, void *stream);
+
+/* forward, eval mode (validate(), imagenet.py:176,187): y = act(gamma*(x-rm)/sqrt(rv+eps)+beta [+z]),
+ * one launch, no statistics. */
+int b200_bn_fwd_eval(const void *x, const void *z, void *y, const float *gamma, const float *beta,
+                     const float *running_mean, const float *running_var, int64_t m, int c, float eps, int act,
+                     int dtype, void *stream);
+
+/* backward (loss.backward(), imagenet.py:128; cudnn/native batch_norm_backward + threshold_backward
+ * + the add's two-way gradient):  dyh = dy*[pre-activation > 0] (ACT_NONE: dyh = dy)
+ *     dbeta = sum dyh ; dgamma = invstd * sum dyh*(x-mean)
+ *     dx = gamma*invstd*(dyh - dbeta/M - (x-mean)*invstd^2*sum(dyh*(x-mean))/M) ;  dz = dyh
+ * three launches (per-chunk sums -> finalize -> apply).  The ReLU mask is recomputed from x and
+ * saved{scale,shift} for B200_ACT_RELU, read from `mask` for B200_ACT_ADD_RELU.  dgamma/dbeta are
+ * written (not accumulated) as float32 - they may point straight into a flat gradient buffer.
+ */
+int b200_bn_bwd(const void *dy, const void *x, const uint8_t *mask, const float *gamma, const float *saved,
+                void *dx, void *dz, float *dgamma, float *dbeta, void *workspace, size_t workspace_bytes,
+                int64_t m, int c, int act, int dtype, void *stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * K1  input stage: crop box -> antialiased bilinear resize -> horizontal flip -> /255 ->
+ * (x-mean)/std -> cast, from uint8 NHWC batches, one pass.
+ * Replaces transforms.Compose([Resize((448,448)), ToTensor(), Normalize(.5,.5)]) run on PIL images
+ * in the DataLoader workers (imagenet.py:280-283,350-354) - box = whole image, no flip - and, with
+ * per-sample boxes/flips, torchvision RandomResizedCrop + RandomHorizontalFlip
+ * (transforms.py:928-981,712-722).  The resize is Pillow's 8-bit BILINEAR resample (Resample.c:
+ * double-precision triangle weights -> 22-bit fixed point, horizontal pass rounded to uint8, then
+ * vertical pass rounded to uint8), reproduced bit for bit; the normalisation is evaluated in float32
+ * with IEEE division exactly as ToTensor/Normalize do, then rounded once to the output dtype.
+ *   images : uint8 [n, src_h, src_w, 3]
+ *   boxes  : int32 [n,4] rows (top, left, height, width), inside the image, on the DEVICE
+ *   flips  : uint8 [n] (non-zero = mirror), on the DEVICE
+ *   out    : [n,out_h,out_w,3] (B200_LAYOUT_NHWC) or [n,3,out_h,out_w] (B200_LAYOUT_NCHW)
+ *   mean3/std3 : HOST pointers to 3 floats each
+ * two launches (coefficient tables into workspace, then the resample).  Down-scaling is limited to
+ * src/out <= 8 per axis.
+ */
+size_t b200_input_workspace_bytes(int64_t n, int src_h, int src_w, int out_h, int out_w);
+int b200_input_crop_resize_flip_norm(const uint8_t *images, const int32_t *boxes, const uint8_t *flips, void *out,
+                                     void *workspace, size_t workspace_bytes, int64_t n, int src_h, int src_w,
+                                     int out_h, int out_w, const float *mean3, const float *std3, int out_dtype,
+                                     int out_layout, void *stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200_IMAGENET_H_ */
