@@ -1,0 +1,271 @@
+#!/usr/bin/env python
+"""Benchmark of the data-parallel training step (BASELINE.json: ResNet-50 train images/sec).
+
+    python bench.py [--gpus N --steps K --warmup W] [--arch resnet50 --batch 256]
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 \
+        --master-port P bench.py --gpus N --steps K --warmup W
+    python bench.py --impl reference ...      # the reference's step on the host cores
+
+One "step" = input kernel (uint8 NHWC -> crop/resize/flip/normalise -> bf16 NHWC) + forward + fused
+CE/top-k + hand-written backward (bucketed NCCL all-reduce overlapped) + fused SGD, on one batch of
+256 synthetic images per GPU.  Prints ONE JSON line on rank 0 (see the keys at the bottom).
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "ResNet-50 train images/sec"
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--arch", default="resnet50")
+    ap.add_argument("--batch", type=int, default=256, help="images per GPU per step")
+    ap.add_argument("--image", type=int, default=224)
+    ap.add_argument("--src", type=int, default=256, help="synthetic source image size (uint8 HxWx3)")
+    ap.add_argument("--fp32", action="store_true")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--ref-batch", type=int, default=16, help="bounded CPU sample: images per reference step")
+    return ap.parse_args()
+
+
+def workload_name(a):
+    return (f"{a.arch} {'fp32' if a.fp32 else 'bf16'} batch {a.batch}/GPU, {a.image}x{a.image} crops of "
+            f"{a.src}x{a.src} uint8 synthetic ImageNet, SGD momentum 0.9 wd 1e-4")
+
+
+# ------------------------------------------------------------------------------------------------
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled every 200 ms while the timed region runs."""
+
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.rows, self.proc, self.index = [], None, index
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "200"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        self.t.join(timeout=2)
+        sm = sorted(int(float(r[0])) for r in self.rows if r and r[0].replace(".", "").isdigit())
+        mx = [int(float(r[1])) for r in self.rows if len(r) > 1 and r[1].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = sorted({n for r in self.rows if len(r) >= 7 for n, v in zip(names, r[3:7]) if v == "Active"})
+        pw = [float(r[2]) for r in self.rows if len(r) > 2 and r[2].replace(".", "").isdigit()]
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": mx[0] if mx else None,
+                "reasons": reasons, "samples": len(sm), "power_w_max": max(pw) if pw else None}
+
+
+def measured_peaks():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            p = json.load(f)
+        return float(p["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+def traffic_per_launch(family):
+    """dram bytes per launch of the dominant kernel family from the committed ncu capture, if any."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
+            return json.load(f).get(family)
+    except Exception:
+        return None
+
+
+# ------------------------------------------------------------------------------------------------
+def run_reference(a):
+    """The reference's own step (imagenet.py:97-151) restated for CPU (oracle/train_cpu.py), stock
+    torch modules, all host threads, on a bounded sample (``--ref-batch`` images per step)."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    from oracle import train_cpu
+
+    r = train_cpu.time_reference_step(a.arch, a.ref_batch, a.image, a.steps, a.warmup)
+    v = r["images_per_sec"]
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": v, "unit": "images/s", "n_gpus": a.gpus, "steps": a.steps,
+        "warmup": a.warmup, "ms_per_step": r["ms_per_step"], "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": workload_name(a), "reference_arm": "CPU restatement of train() (oracle port), "
+                   "stock DDP-less single process, fp32 NCHW"},
+        "cpu_baseline": {"value": v, "unit": "images/s", "cores": r["cores"], "kind": "port", "sample": r["sample"]},
+        "e2e": {"value": v, "unit": "images/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }))
+
+
+def run_ours(a):
+    import torch
+    import torch.distributed as dist
+
+    import imagent_distributed_training_pytorch_with_slurm_b200 as b200
+    from imagent_distributed_training_pytorch_with_slurm_b200 import _cabi
+
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+    torch.backends.cudnn.benchmark = True
+    dtype = torch.float32 if a.fp32 else torch.bfloat16
+
+    torch.manual_seed(0)
+    model = b200.FlatDDP(b200.build_model(a.arch, 1000, dev, dtype).cuda(), device_ids=[local], output_device=local)
+    crit = b200.CrossEntropyLoss().cuda()
+    opt = b200.FlatSGD(model.parameters(), 0.1, momentum=0.9, weight_decay=1e-4)
+    b200.adjust_learning_rate(0.1, opt, 0)
+    model.train()
+
+    # ---- device-resident inputs (value): everything the step reads is in HBM before timing -------
+    total = a.warmup + a.steps
+    g = torch.Generator().manual_seed(1234 + rank)
+    images = torch.randint(0, 256, (a.batch, a.src, a.src, 3), dtype=torch.uint8, generator=g).to(dev)
+    params = []
+    box_bytes = 0
+    for _ in range(total):
+        boxes, flips = b200.draw_batch_params(a.batch, a.src, a.src, g)
+        tgt = torch.randint(0, 1000, (a.batch,), dtype=torch.int64, generator=g)
+        box_bytes += int((boxes[:, 2].long() * boxes[:, 3].long()).sum()) * 3
+        params.append((boxes.to(dev), flips.to(dev), tgt.to(dev)))
+    mean, std = b200.data.IMAGENET_MEAN, b200.data.IMAGENET_STD
+
+    def step(i):
+        boxes, flips, tgt = params[i]
+        x = _cabi.input_stage(images, boxes, flips, a.image, a.image, mean, std, dtype)
+        logits = model(x)
+        loss = crit(logits, tgt)
+        opt.zero_grad()
+        loss.backward()
+        opt.step()
+        return loss
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for i in range(a.warmup):
+        step(i)
+    barrier()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    _cabi.stats.reset()
+    _cabi.stats.timed = {"input", "bn_fwd", "bn_bwd", "ce_topk_fwd", "ce_bwd", "sgd"}
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for i in range(a.warmup, total):
+        loss = step(i)
+    e1.record()
+    barrier()
+    _cabi.stats.timed = None
+    ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
+    if world > 1:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    ms_total = float(ms.item())
+    launches = _cabi.stats.launches
+    fam = _cabi.stats.summary()
+    final_loss = float(loss.item())
+    value = a.batch * world * a.steps / (ms_total / 1e3)
+
+    # ---- end to end through the public API with HOST buffers ------------------------------------
+    e2e = None
+    if not a.no_e2e:
+        wl = b200.SyntheticImageNet(a.batch, max(a.warmup, 1), a.src, a.image, rank=rank, dtype=dtype, host=True)
+        tl = b200.SyntheticImageNet(a.batch, a.steps, a.src, a.image, rank=rank, dtype=dtype, host=True)
+        b200.train(wl, model, crit, opt, 0, world, sync_every=1)
+        barrier()
+        t0 = time.perf_counter()
+        b200.train(tl, model, crit, opt, 0, world, sync_every=1)  # every step: H2D of the batch, D2H of the loss
+        barrier()
+        dt = torch.tensor([time.perf_counter() - t0], device=dev)
+        if world > 1:
+            dist.all_reduce(dt, op=dist.ReduceOp.MAX)
+        e2e = {"value": a.batch * world * a.steps / float(dt.item()), "unit": "images/s",
+               "h2d_bytes_per_step": tl.h2d_bytes, "d2h_bytes_per_step": 12}
+    clocks = sampler.stop() if rank == 0 else None
+
+    if rank == 0:
+        peak, peak_src = measured_peaks()
+        kernels = {}
+        for name, d in fam.items():
+            nbytes = d["bytes"] + (box_bytes * a.steps // total if name == "input" else 0)
+            kernels[name] = {"calls": d["calls"], "ms_per_step": d["ms"] / a.steps,
+                             "algorithmic_GB_per_step": nbytes / a.steps / 1e9,
+                             "GBps": nbytes / 1e9 / (d["ms"] / 1e3) if d["ms"] > 0 else None}
+        hbm = {k: v for k, v in kernels.items() if k in ("bn_fwd", "bn_bwd", "sgd", "input")}
+        dom = max(hbm, key=lambda k: hbm[k]["ms_per_step"]) if hbm else None
+        roof = None
+        if dom:
+            ach = hbm[dom]["GBps"]
+            roof = {"kernel": dom, "bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s",
+                    "frac": ach / peak if ach else None, "traffic": traffic_per_launch(dom),
+                    "peak_source": peak_src, "launches_per_step": hbm[dom]["calls"] / a.steps,
+                    "share_of_step": hbm[dom]["ms_per_step"] / (ms_total / a.steps)}
+        cpu = None
+        if world == 1 and not a.no_cpu_baseline:
+            from oracle import train_cpu
+
+            r = train_cpu.time_reference_step(a.arch, a.ref_batch, a.image, 6, 1)
+            cpu = {"value": r["images_per_sec"], "unit": "images/s", "cores": r["cores"], "kind": "port",
+                   "sample": r["sample"]}
+        out = {
+            "metric": METRIC, "value": value, "unit": "images/s", "n_gpus": world, "steps": a.steps,
+            "warmup": a.warmup, "ms_per_step": ms_total / a.steps, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f32" if a.fp32 else "bf16", "data": "synthetic",
+            "config": {"workload": workload_name(a), "arch": a.arch, "per_gpu_batch": a.batch,
+                       "global_batch": a.batch * world, "image": a.image, "parallelism": f"dp{world}",
+                       "l2": "not flushed: one step streams >10 GB of activations, far larger than the 126 MB L2"},
+            "e2e": e2e, "gpu_launches": launches, "clocks": clocks, "roofline": roof, "cpu_baseline": cpu,
+            "kernels": kernels, "final_loss": final_loss,
+        }
+        print(json.dumps(out))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    args = parse()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)

@@ -91,10 +91,15 @@ class DeviceInputStage:
 
 class SyntheticImageNet:
     """Iterable of (input, target) like the reference's DataLoader (imagenet.py:350-354), over
-    synthetic uint8 images.  ``host=True`` keeps the batch in pinned host memory and copies it every
-    step (end-to-end path); ``host=False`` keeps it resident in HBM.  Images are seeded per rank
-    (``seed + rank``); one fixed image batch is re-used, the crop boxes / flips / targets are drawn per
-    step unless ``fixed_params``."""
+    synthetic uint8 images.
+
+    ``host=True`` keeps the image batch in pinned host memory and copies it to the GPU EVERY step
+    (the end-to-end path: what ``pin_memory=True`` + ``.cuda(non_blocking=True)`` do in the
+    reference, imagenet.py:119,354), double-buffered on a side stream so the copy of step i+1 overlaps
+    the compute of step i.  ``host=False`` keeps the images resident in HBM.  Images are seeded per
+    rank (``seed + rank``); one fixed image batch is re-used, the crop boxes / flips / targets are
+    drawn per step from the same generator unless ``fixed_params``.
+    """
 
     def __init__(self, batch_size, steps, src_size=256, out_size=224, num_classes=1000, rank=0, seed=1234,
                  random_crop=True, mean=IMAGENET_MEAN, std=IMAGENET_STD, dtype=torch.bfloat16, host=False,
@@ -106,9 +111,16 @@ class SyntheticImageNet:
         self.gen.manual_seed(seed + rank)
         self.stage = DeviceInputStage(out_size, mean, std, dtype, device)
         img = torch.randint(0, 256, (batch_size, self.src_h, self.src_w, 3), dtype=torch.uint8, generator=self.gen)
-        self.images = img.pin_memory() if host else img.to(self.stage.device)
+        dev = self.stage.device
+        if host:
+            self.images = img.pin_memory()
+            self._stream = torch.cuda.Stream(device=dev)
+            self._slots = [{"img": torch.empty_like(img, device=dev), "ready": torch.cuda.Event(),
+                            "free": torch.cuda.Event()} for _ in range(2)]
+        else:
+            self.images = img.to(dev)
         self._fixed = None
-        self.h2d_bytes = 0
+        self.h2d_bytes = (img.numel() if host else 0) + batch_size * (16 + 1 + 8)
 
     def __len__(self):
         return self.steps
@@ -123,10 +135,38 @@ class SyntheticImageNet:
             self._fixed = out
         return out
 
+    def _upload(self, slot, first_use):
+        """Enqueue the H2D copies of one step on the side stream."""
+        dev = self.stage.device
+        boxes, flips, target = self._params()
+        with torch.cuda.stream(self._stream):
+            if not first_use:
+                self._stream.wait_event(slot["free"])  # the kernel that read this slot has finished
+            slot["img"].copy_(self.images, non_blocking=True)
+            slot["boxes"] = boxes.to(dev, non_blocking=True)
+            slot["flips"] = flips.to(dev, non_blocking=True)
+            slot["target"] = target.to(dev, non_blocking=True)
+            slot["ready"].record(self._stream)
+
     def __iter__(self):
-        for _ in range(self.steps):
-            boxes, flips, target = self._params()
-            x = self.stage(self.images, boxes, flips)
-            self.h2d_bytes = (self.images.numel() if self.host else 0) + boxes.numel() * 4 + flips.numel() + \
-                target.numel() * 8
-            yield x, target.to(self.stage.device, non_blocking=True)
+        dev = self.stage.device
+        if not self.host:
+            for _ in range(self.steps):
+                boxes, flips, target = self._params()
+                x = self.stage(self.images, boxes, flips)
+                yield x, target.to(dev, non_blocking=True)
+            return
+        main = torch.cuda.current_stream(dev)
+        if self.steps > 0:
+            self._upload(self._slots[0], True)
+        for i in range(self.steps):
+            slot = self._slots[i % 2]
+            if i + 1 < self.steps:
+                self._upload(self._slots[(i + 1) % 2], i + 1 < 2)
+            main.wait_event(slot["ready"])
+            x = _cabi.input_stage(slot["img"], slot["boxes"], slot["flips"], self.stage.out_h, self.stage.out_w,
+                                  self.stage.mean, self.stage.std, self.stage.dtype, self.stage.layout)
+            slot["free"].record(main)
+            for k in ("boxes", "flips", "target"):
+                slot[k].record_stream(main)
+            yield x, slot["target"]

@@ -1,0 +1,43 @@
+"""The C-ABI library loads and exports every symbol include/b200_imagenet.h declares (no compute)."""
+import ctypes
+import os
+import re
+
+import imagent_distributed_training_pytorch_with_slurm_b200._cabi as cabi
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _declared():
+    src = open(os.path.join(ROOT, "include", "b200_imagenet.h")).read()
+    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+    return sorted(set(re.findall(r"\b(b200_[a-z0-9_]+)\s*\(", src)))
+
+
+def test_library_exports_every_declared_symbol():
+    names = _declared()
+    assert len(names) >= 14
+    lib = ctypes.CDLL(cabi.LIB_PATH)
+    for n in names:
+        assert hasattr(lib, n), n
+    assert set(names) == set(cabi.SIGNATURES), set(names) ^ set(cabi.SIGNATURES)
+
+
+def test_binding_loads_and_reports_version_and_sizes():
+    lib = cabi.load()
+    assert lib.b200_abi_version() == cabi.ABI_VERSION
+    assert lib.b200_error_string(1).decode().lower().startswith("invalid")
+    assert lib.b200_ce_topk_workspace_bytes(256) == 16 + 12 * 256
+    assert lib.b200_bn_workspace_bytes(256 * 56 * 56, 64, cabi.BF16) > 0
+    assert lib.b200_input_workspace_bytes(4, 256, 256, 224, 224) > 0
+    assert lib.b200_bn_vec(cabi.F32) == 4 and lib.b200_bn_vec(cabi.BF16) in (4, 8)
+    assert lib.b200_tune_set(b"no_such_key", 1) != 0
+
+
+def test_argument_errors_are_reported_not_crashed():
+    lib = cabi.load()
+    # null pointers / bad sizes are rejected before any launch
+    assert lib.b200_sgd_flat_f32(None, None, None, None, 16, 0.1, 0.0, 0.9, 1.0, 0, None) == 1
+    assert lib.b200_ce_topk_fwd(None, None, None, None, None, 0, 4, 10, 0, None) == 1
+    assert lib.b200_bn_fwd_train(None, None, None, None, None, None, None, None, None, None, None, 0, 8, 6, 1e-5, 0.1,
+                                 0, 1, None) == 1  # C=6 not a multiple of the bf16 vector width

@@ -1,0 +1,329 @@
+"""Parity of every CUDA kernel with the oracle, called through the C ABI (ctypes).  -m gpu only.
+
+Tolerances (stated per test): integer/byte results bit-exact; float32-I/O kernels within a few ulp /
+1e-5 relative of the float64-accumulating oracle; bf16-I/O kernels within bf16 rounding of it.
+"""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import batchnorm as obn
+from oracle import cross_entropy as oce
+from oracle import input_pipeline as oin
+from oracle import sgd as osgd
+
+import imagent_distributed_training_pytorch_with_slurm_b200._cabi as cabi
+
+pytestmark = pytest.mark.gpu
+GOLD = os.path.join(os.path.dirname(__file__), "golden")
+DEV = "cuda"
+
+
+def _bf16_round(a):
+    return torch.from_numpy(np.asarray(a, dtype=np.float32)).to(torch.bfloat16).float().numpy()
+
+
+# ------------------------------------------------------------------------------------------------ K4b
+@pytest.mark.parametrize("n", [1, 3, 4099, 1 << 20, 25_557_032])
+@pytest.mark.parametrize("shadow", [False, True])
+def test_sgd_flat_matches_oracle(n, shadow):
+    rng = np.random.default_rng(n)
+    p0 = rng.standard_normal(n).astype(np.float32)
+    p = torch.from_numpy(p0.copy()).to(DEV)
+    buf = torch.zeros(n, device=DEV)
+    sh = torch.zeros(n, dtype=torch.bfloat16, device=DEV) if shadow else None
+    po, bo = p0, None
+    for step in range(3):
+        g0 = rng.standard_normal(n).astype(np.float32)
+        g = torch.from_numpy(g0).to(DEV)
+        cabi.sgd_flat(p, g, buf, sh, 0.1, 1e-4, 0.9, 1.0, step == 0)
+        prev = po
+        po, bo = osgd.sgd_step_oracle(po, g0, bo, 0.1, 0.9, 1e-4, first_step=(step == 0))
+        big = np.maximum(np.maximum(np.abs(prev), np.abs(po)), np.abs(bo)).astype(np.float32)
+        tol = 2 * np.spacing(big)  # <= 2 ulp of the largest operand (fused vs separate multiply-add)
+        assert (np.abs(p.cpu().numpy() - po) <= tol).all(), step
+        assert (np.abs(buf.cpu().numpy() - bo) <= tol).all(), step
+        # keep the two trajectories from drifting apart by rounding: continue from the GPU state
+        po, bo = p.cpu().numpy(), buf.cpu().numpy()
+        if shadow:
+            assert torch.equal(sh, p.to(torch.bfloat16))
+
+
+def test_sgd_golden_trajectory_and_grad_scale():
+    c = np.load(os.path.join(GOLD, "sgd_case.npz"))
+    p = torch.from_numpy(c["p0"].copy()).to(DEV)
+    buf = torch.zeros_like(p)
+    for s in range(len(c["grads"])):
+        g = torch.from_numpy(c["grads"][s] * 4.0).to(DEV)  # un-averaged sum of 4 ranks ...
+        cabi.sgd_flat(p, g, buf, None, 0.1, 1e-4, 0.9, 0.25, s == 0)  # ... scaled back by 1/world
+        assert np.allclose(p.cpu().numpy(), c["ps"][s], rtol=0, atol=4e-7 * (s + 1))
+
+
+# ------------------------------------------------------------------------------------------------ K3
+def _ce_case(n, c, seed, dtype):
+    g = torch.Generator().manual_seed(seed)
+    x = torch.randn(n, c, generator=g) * 3.0
+    t = torch.randint(0, c, (n,), generator=g)
+    for r in range(0, n, 3):
+        x[r, t[r]] += 7.0
+    for r in range(1, n, 4):
+        x[r, t[r]] += 2.0
+    return x.to(dtype), t
+
+
+@pytest.mark.parametrize("n,c", [(1, 8), (7, 13), (64, 1000), (256, 1000), (33, 1001), (5, 4099)])
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_ce_topk_matches_oracle(n, c, dtype):
+    x, t = _ce_case(n, c, n * 31 + c, dtype)
+    xo = x.float().numpy()  # the oracle sees exactly the values the kernel sees
+    loss, t1, t5, dl, lse = oce.ce_topk_oracle(xo, t.numpy())
+    out3, row_lse = cabi.ce_topk_fwd(x.to(DEV), t.to(DEV))
+    out3 = out3.cpu().numpy()
+    assert abs(out3[0] - loss) <= 2e-6 * abs(loss)         # float32 accumulation vs float64
+    assert out3[1] == t1 and out3[2] == t5                 # counts: bit-exact
+    assert np.allclose(row_lse.cpu().numpy(), lse, rtol=2e-6, atol=2e-6)
+    gout = torch.tensor(0.5, device=DEV)
+    d = cabi.ce_bwd(x.to(DEV), t.to(DEV), row_lse, gout, 2.0).float().cpu().numpy()  # 0.5 * 2.0 = 1
+    if dtype == torch.float32:
+        assert np.abs(d - dl).max() <= 2e-7
+    else:
+        assert np.abs(d - dl).max() <= np.abs(dl).max() * 2 ** -8 + 1e-9  # one bf16 rounding
+
+
+def test_ce_topk_golden_reference_accuracy():
+    c = np.load(os.path.join(GOLD, "ce_topk_case.npz"))
+    out3, _ = cabi.ce_topk_fwd(torch.from_numpy(c["logits"]).to(DEV), torch.from_numpy(c["target"]).to(DEV))
+    out3 = out3.cpu().numpy()
+    assert out3[1] == c["prec1"] and out3[2] == c["prec5"]  # the reference's accuracy() output
+    assert abs(out3[0] - c["loss"]) <= 2e-6 * c["loss"]
+
+
+def test_ce_topk_ties_and_determinism():
+    # all-equal rows: the target ranks behind the classes with a lower index
+    x = torch.zeros(6, 16, device=DEV)
+    t = torch.tensor([0, 1, 4, 5, 15, 3], device=DEV)
+    out3, _ = cabi.ce_topk_fwd(x, t)
+    o = out3.cpu().numpy()
+    assert o[1] == np.float32(100.0 / 6) * 1 and o[2] == np.float32(np.float32(4) * np.float32(100.0 / 6))
+    assert abs(o[0] - np.log(16.0)) < 1e-6
+    x, t = _ce_case(256, 1000, 5, torch.bfloat16)
+    a = cabi.ce_topk_fwd(x.to(DEV), t.to(DEV))[0].clone()
+    for _ in range(5):
+        b = cabi.ce_topk_fwd(x.to(DEV), t.to(DEV))[0]
+        assert torch.equal(a, b)  # fixed-order reduction: bit-reproducible
+
+
+# ------------------------------------------------------------------------------------------------ K2
+def _rows_t(a, dtype):  # [M, C] numpy -> device tensor
+    return torch.from_numpy(np.ascontiguousarray(a)).to(dtype).to(DEV)
+
+
+def _bn_check(m, c, act, dtype, vec, seed, eps=1e-5, momentum=0.1):
+    if dtype == torch.bfloat16:
+        cabi.tune_set("bn_vec_bf16", vec)
+    rng = np.random.default_rng(seed)
+    x = (rng.standard_normal((m, c)) * rng.uniform(0.5, 2.0, c) + rng.uniform(-3, 3, c)).astype(np.float32)
+    z = rng.standard_normal((m, c)).astype(np.float32)
+    dy = rng.standard_normal((m, c)).astype(np.float32)
+    gamma = rng.uniform(0.5, 1.5, c).astype(np.float32)
+    beta = (rng.standard_normal(c) * 0.3).astype(np.float32)
+    rm0, rv0 = rng.standard_normal(c).astype(np.float32), rng.uniform(0.5, 2, c).astype(np.float32)
+    xd, zd, dyd = _rows_t(x, dtype), _rows_t(z, dtype), _rows_t(dy, dtype)
+    xs, zs, dys = xd.float().cpu().numpy(), zd.float().cpu().numpy(), dyd.float().cpu().numpy()
+    gd, bd = torch.from_numpy(gamma).to(DEV), torch.from_numpy(beta).to(DEV)
+    rm, rv = torch.from_numpy(rm0.copy()).to(DEV), torch.from_numpy(rv0.copy()).to(DEV)
+    nbt = torch.tensor(5, dtype=torch.int64, device=DEV)
+    y, saved, mask = cabi.bn_fwd_train(xd, zd if act == cabi.ACT_ADD_RELU else None, gd, bd, rm, rv, nbt, eps,
+                                       momentum, act)
+    yo, mean, invstd, rmo, rvo, pos = obn.bn_train_fwd_oracle(xs, gamma, beta, rm0, rv0, eps, momentum, act, zs)
+    bf = dtype == torch.bfloat16
+    sv = saved.cpu().numpy()
+    assert np.allclose(sv[0], mean, rtol=1e-5, atol=1e-5)
+    assert np.allclose(sv[1], invstd, rtol=2e-5)
+    assert np.allclose(rm.cpu().numpy(), rmo, rtol=1e-5, atol=1e-5)
+    assert np.allclose(rv.cpu().numpy(), rvo, rtol=2e-5, atol=1e-6)
+    assert int(nbt) == 6
+    yk = y.float().cpu().numpy()
+    if bf:
+        assert np.abs(yk - yo).max() <= np.abs(yo).max() * 2 ** -7
+    else:
+        assert np.allclose(yk, yo, rtol=2e-5, atol=2e-5)
+    # backward, fed with the kernel's own saved statistics.  Elements whose pre-activation is within
+    # rounding of zero may take either side of the ReLU (float32 fma in the kernel vs float64 in the
+    # oracle); they are excluded from the element-wise checks and bounded in number.
+    dx, dz, dg, db = cabi.bn_bwd(dyd, xd, mask, gd, saved, act)
+    dxo, dzo, dgo, dbo = obn.bn_train_bwd_oracle(dys, xs, gamma, mean, invstd, act, pos)
+    pre = (xs.astype(np.float64) - mean) * invstd * gamma + beta + (zs if act == cabi.ACT_ADD_RELU else 0.0)
+    safe = (np.abs(pre) > 1e-4) if act != cabi.ACT_NONE else np.ones_like(pre, dtype=bool)
+    assert (~safe).mean() < 1e-3
+    scale = np.abs(dgo).max() + np.abs(dbo).max()
+    assert np.allclose(db.cpu().numpy(), dbo, rtol=1e-4, atol=1e-4 * scale + 1e-3)
+    assert np.allclose(dg.cpu().numpy(), dgo, rtol=1e-4, atol=1e-4 * scale + 1e-3)
+    dxk = dx.float().cpu().numpy()
+    if bf:
+        assert (np.abs(dxk - dxo)[safe]).max() <= np.abs(dxo).max() * 2 ** -7
+    else:
+        assert np.allclose(dxk[safe], dxo[safe], rtol=1e-4, atol=1e-5 * (np.abs(dxo).max() + 1))
+    if act == cabi.ACT_ADD_RELU:
+        assert np.array_equal(dz.float().cpu().numpy()[safe], (dys * pos)[safe])  # masked copy: exact
+    # eval mode with the updated running statistics
+    ye = cabi.bn_fwd_eval(xd, zd if act == cabi.ACT_ADD_RELU else None, gd, bd, rm, rv, eps, act)
+    yeo = obn.bn_eval_fwd_oracle(xs, gamma, beta, rm.cpu().numpy(), rv.cpu().numpy(), eps, act, zs)
+    if bf:
+        assert np.abs(ye.float().cpu().numpy() - yeo).max() <= np.abs(yeo).max() * 2 ** -7
+    else:
+        assert np.allclose(ye.cpu().numpy(), yeo, rtol=2e-5, atol=2e-5)
+
+
+SHAPES = [(2, 8), (210, 16), (1000, 64), (4099, 24), (777, 256), (300, 2048), (50176, 64), (12544, 512), (3, 40)]
+
+
+@pytest.mark.parametrize("m,c", SHAPES)
+@pytest.mark.parametrize("act", [cabi.ACT_NONE, cabi.ACT_RELU, cabi.ACT_ADD_RELU])
+def test_bn_f32_matches_oracle(m, c, act):
+    _bn_check(m, c, act, torch.float32, 4, seed=m + c + act)
+
+
+@pytest.mark.parametrize("m,c", SHAPES)
+@pytest.mark.parametrize("act", [cabi.ACT_NONE, cabi.ACT_RELU, cabi.ACT_ADD_RELU])
+@pytest.mark.parametrize("vec", [4, 8])
+def test_bn_bf16_matches_oracle(m, c, act, vec):
+    if c % vec:
+        pytest.skip("channel count not a multiple of the vector width")
+    try:
+        _bn_check(m, c, act, torch.bfloat16, vec, seed=m + c + act)
+    finally:
+        cabi.tune_set("bn_vec_bf16", 8)
+
+
+def test_bn_golden_case_from_torch():
+    c = np.load(os.path.join(GOLD, "bn_case.npz"))
+
+    def cl(a):
+        return torch.from_numpy(a).to(DEV).contiguous(memory_format=torch.channels_last)
+
+    x, z, dy = cl(c["x"]), cl(c["z"]), cl(c["dy"])
+    g, b = torch.from_numpy(c["gamma"]).to(DEV), torch.from_numpy(c["beta"]).to(DEV)
+    for name, act in (("none", 0), ("relu", 1), ("add_relu", 2)):
+        rm, rv = torch.zeros(16, device=DEV), torch.ones(16, device=DEV)
+        nbt = torch.zeros((), dtype=torch.int64, device=DEV)
+        y, saved, mask = cabi.bn_fwd_train(x, z if act == 2 else None, g, b, rm, rv, nbt, 1e-5, 0.1, act)
+        assert y.shape == x.shape and y.is_contiguous(memory_format=torch.channels_last)
+        assert np.allclose(y.cpu().numpy(), c[f"{name}_y"], rtol=1e-5, atol=1e-5)
+        dx, dz, dg, db = cabi.bn_bwd(dy, x, mask, g, saved, act)
+        assert np.allclose(dx.cpu().numpy(), c[f"{name}_dx"], rtol=1e-4, atol=1e-5)
+        assert np.allclose(dg.cpu().numpy(), c[f"{name}_dgamma"], rtol=1e-4, atol=1e-4)
+        assert np.allclose(db.cpu().numpy(), c[f"{name}_dbeta"], rtol=1e-4, atol=1e-4)
+        if act == 2:
+            assert np.allclose(dz.cpu().numpy(), c["add_relu_dz"], rtol=1e-6, atol=1e-6)
+    assert np.allclose(rm.cpu().numpy(), c["running_mean"], rtol=1e-5, atol=1e-6)
+    assert np.allclose(rv.cpu().numpy(), c["running_var"], rtol=1e-5, atol=1e-6)
+    assert int(nbt) == 1
+
+
+def test_bn_large_mean_does_not_cancel():
+    """|mean| >> std: the shifted-sum statistics must not lose the variance."""
+    m, c = 8192, 64
+    rng = np.random.default_rng(0)
+    x = (rng.standard_normal((m, c)) * 0.01 + 100.0).astype(np.float32)
+    xd = torch.from_numpy(x).to(DEV)
+    g, b = torch.ones(c, device=DEV), torch.zeros(c, device=DEV)
+    _, saved, _ = cabi.bn_fwd_train(xd, None, g, b, torch.zeros(c, device=DEV), torch.ones(c, device=DEV), None, 1e-5,
+                                    0.1, 0)
+    var = x.astype(np.float64).var(axis=0)
+    invstd = 1.0 / np.sqrt(var + 1e-5)
+    assert np.allclose(saved[1].cpu().numpy(), invstd, rtol=1e-3)
+
+
+@pytest.mark.parametrize("shape", [(256, 64, 112, 112), (256, 256, 56, 56), (256, 2048, 7, 7)])
+def test_bn_full_size_properties(shape):
+    """BASELINE sizes (ResNet-50, N=256, bf16): checked through properties that do not need the
+    oracle to chew 0.8 G elements - normalised output has zero mean / unit variance per channel,
+    dbeta = sum(dy), dx is orthogonal to 1 and to x-hat."""
+    n, c, h, w = shape
+    g = torch.Generator(device=DEV).manual_seed(1)
+    x = (torch.randn(n, h, w, c, device=DEV, generator=g) * 1.5 + 0.7).to(torch.bfloat16).permute(0, 3, 1, 2)
+    dy = torch.randn(n, h, w, c, device=DEV, generator=g).to(torch.bfloat16).permute(0, 3, 1, 2)
+    gamma, beta = torch.ones(c, device=DEV), torch.zeros(c, device=DEV)
+    rm, rv = torch.zeros(c, device=DEV), torch.ones(c, device=DEV)
+    y, saved, _ = cabi.bn_fwd_train(x, None, gamma, beta, rm, rv, None, 1e-5, 0.1, cabi.ACT_NONE)
+    yf = y.float()
+    assert yf.mean((0, 2, 3)).abs().max().item() < 3e-3
+    assert (yf.pow(2).mean((0, 2, 3)) - 1).abs().max().item() < 1e-2
+    xf = x.float()
+    assert torch.allclose(saved[0], xf.mean((0, 2, 3)), rtol=1e-4, atol=1e-4)
+    dx, _, dg, db = cabi.bn_bwd(dy, x, None, gamma, saved, cabi.ACT_NONE)
+    m = n * h * w
+    assert torch.allclose(db, dy.float().sum((0, 2, 3)), rtol=1e-3, atol=1e-3 * m ** 0.5)
+    dxf = dx.float()
+    assert (dxf.sum((0, 2, 3)).abs() / m).max().item() < 1e-3           # sum(dx) = 0
+    xhat = (xf - saved[0].view(1, c, 1, 1)) * saved[1].view(1, c, 1, 1)
+    assert ((dxf * xhat).sum((0, 2, 3)).abs() / m).max().item() < 1e-2  # sum(dx * xhat) = 0
+
+
+# ------------------------------------------------------------------------------------------------ K1
+def _run_input(images, boxes, flips, oh, ow, mean, std, dtype, layout):
+    out = cabi.input_stage(torch.from_numpy(images).to(DEV), torch.from_numpy(np.asarray(boxes, dtype=np.int32)).to(DEV),
+                           torch.from_numpy(np.asarray(flips, dtype=np.uint8)).to(DEV), oh, ow, mean, std, dtype, layout)
+    return out.float().cpu().permute(0, 2, 3, 1).numpy()  # logical NCHW -> NHWC values
+
+
+def test_input_stage_golden_bit_exact():
+    c = np.load(os.path.join(GOLD, "input_case.npz"))
+    n = len(c["images"])
+    full = np.tile(np.array([[0, 0, 96, 80]], dtype=np.int32), (n, 1))
+    for layout in (cabi.LAYOUT_NHWC, cabi.LAYOUT_NCHW):
+        out = _run_input(c["images"], full, np.zeros(n), 56, 56, (.5, .5, .5), (.5, .5, .5), torch.float32, layout)
+        assert np.array_equal(out, c["ref_mode_out"])      # reference mode == torchvision on PIL, bit-exact
+        out = _run_input(c["images"], c["boxes"], c["flips"], 48, 48, c["rrc_mean"].tolist(), c["rrc_std"].tolist(),
+                         torch.float32, layout)
+        assert np.array_equal(out, c["rrc_out"])           # crop + resize + flip + normalise, bit-exact
+    out = _run_input(c["images"], c["boxes"], c["flips"], 48, 48, c["rrc_mean"].tolist(), c["rrc_std"].tolist(),
+                     torch.bfloat16, cabi.LAYOUT_NHWC)
+    assert np.array_equal(out, _bf16_round(c["rrc_out"]))  # bf16 = one rounding of the float32 result
+
+
+@pytest.mark.parametrize("sh,sw,oh,ow", [(256, 256, 224, 224), (500, 375, 448, 448), (100, 120, 224, 224),
+                                         (375, 500, 224, 224), (33, 57, 7, 9), (224, 224, 224, 224),
+                                         (640, 480, 96, 96)])
+def test_input_stage_matches_oracle_bit_exact(sh, sw, oh, ow):
+    rng = np.random.default_rng(sh * 7 + sw)
+    n = 5
+    images = rng.integers(0, 256, (n, sh, sw, 3), dtype=np.uint8)
+    g = torch.Generator().manual_seed(sh + sw)
+    from imagent_distributed_training_pytorch_with_slurm_b200.data import draw_batch_params
+    boxes, flips = draw_batch_params(n, sh, sw, g)
+    boxes, flips = boxes.numpy().copy(), flips.numpy().copy()
+    boxes[0] = (0, 0, sh, sw)            # whole image
+    boxes[1] = (sh - 1, sw - 1, 1, 1)    # single-pixel box in the corner (pure up-scaling)
+    boxes[2] = (0, sw // 2, sh, 1)       # one column
+    flips[0], flips[1] = 0, 1
+    mean, std = (0.485, 0.456, 0.406), (0.229, 0.224, 0.225)
+    ref = oin.input_stage_oracle(images, boxes, flips.astype(bool), oh, ow, mean, std)
+    out = _run_input(images, boxes, flips, oh, ow, mean, std, torch.float32, cabi.LAYOUT_NHWC)
+    assert np.array_equal(out, ref)
+
+
+def test_input_stage_full_batch_properties():
+    """BASELINE size (256 x 256x256 -> 224x224 bf16): flip is an exact mirror, and a constant image
+    stays constant through resize and normalisation."""
+    n = 256
+    g = torch.Generator().manual_seed(0)
+    images = torch.randint(0, 256, (n, 256, 256, 3), dtype=torch.uint8, generator=g)
+    images[0] = 77
+    from imagent_distributed_training_pytorch_with_slurm_b200.data import draw_batch_params
+    boxes, _ = draw_batch_params(n, 256, 256, g)
+    dev = images.to(DEV)
+    mean, std = (0.485, 0.456, 0.406), (0.229, 0.224, 0.225)
+    a = cabi.input_stage(dev, boxes.to(DEV), torch.zeros(n, dtype=torch.uint8, device=DEV), 224, 224, mean, std)
+    b = cabi.input_stage(dev, boxes.to(DEV), torch.ones(n, dtype=torch.uint8, device=DEV), 224, 224, mean, std)
+    assert a.is_contiguous(memory_format=torch.channels_last) and a.dtype == torch.bfloat16
+    assert torch.equal(a, b.flip(3))
+    lut = oin.normalize_lut(mean, std)
+    for ch in range(3):
+        assert torch.all(a[0, ch].float() == float(_bf16_round(lut[ch][77])))
+    # three samples against the oracle
+    ref = oin.input_stage_oracle(images[5:8].numpy(), boxes[5:8].numpy(), np.zeros(3, bool), 224, 224, mean, std)
+    assert np.array_equal(a[5:8].float().cpu().permute(0, 2, 3, 1).numpy(), _bf16_round(ref))
