@@ -218,6 +218,8 @@ class B200ResNet(nn.Module):
         if device is None:
             device = torch.device("cuda", torch.cuda.current_device())
         device = torch.device(device)  # kernels raise on non-CUDA tensors: there is no CPU path
+        if device.type == "cuda" and device.index is None:
+            device = torch.device("cuda", torch.cuda.current_device())
         self.arch, self.act_dtype, self.device = arch, dtype, device
 
         self.conv1, self.bn1 = _Conv(tv.conv1), _BN(tv.bn1)

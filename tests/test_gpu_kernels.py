@@ -39,10 +39,10 @@ def test_sgd_flat_matches_oracle(n, shadow):
         g0 = rng.standard_normal(n).astype(np.float32)
         g = torch.from_numpy(g0).to(DEV)
         cabi.sgd_flat(p, g, buf, sh, 0.1, 1e-4, 0.9, 1.0, step == 0)
-        prev = po
+        prev, prev_b = po, (bo if bo is not None else np.zeros_like(po))
         po, bo = osgd.sgd_step_oracle(po, g0, bo, 0.1, 0.9, 1e-4, first_step=(step == 0))
-        big = np.maximum(np.maximum(np.abs(prev), np.abs(po)), np.abs(bo)).astype(np.float32)
-        tol = 2 * np.spacing(big)  # <= 2 ulp of the largest operand (fused vs separate multiply-add)
+        big = np.maximum.reduce([np.abs(prev), np.abs(po), np.abs(bo), np.abs(prev_b), np.abs(g0)]).astype(np.float32)
+        tol = 3 * np.spacing(big)  # <= 3 ulp of the largest operand (fused vs separately rounded multiply-adds)
         assert (np.abs(p.cpu().numpy() - po) <= tol).all(), step
         assert (np.abs(buf.cpu().numpy() - bo) <= tol).all(), step
         # keep the two trajectories from drifting apart by rounding: continue from the GPU state
