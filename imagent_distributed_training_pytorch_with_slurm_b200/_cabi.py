@@ -236,7 +236,8 @@ def bn_fwd_train(x, z, gamma, beta, running_mean, running_var, num_batches_track
     if act == ACT_ADD_RELU:
         assert z is not None and z.shape == x.shape and z.dtype == x.dtype
         _rows_channels(z)
-        mask = torch.empty(m * (c // lib.b200_bn_vec(dt)), dtype=torch.uint8, device=x.device)
+        # +16: the bulk-async backward fetches the mask in 16-byte units and may read past the last byte
+        mask = torch.empty(m * (c // lib.b200_bn_vec(dt)) + 16, dtype=torch.uint8, device=x.device)
     nbytes = lib.b200_bn_workspace_bytes(m, c, dt)
     ws = workspace(x.device, nbytes, "bn")
     s = stats.begin("bn_fwd")
@@ -244,7 +245,7 @@ def bn_fwd_train(x, z, gamma, beta, running_mean, running_var, num_batches_track
                                  _ptr(running_var), _ptr(num_batches_tracked), _ptr(saved), _ptr(ws), ws.numel(), m, c,
                                  eps, momentum, act, dt, _stream()), "b200_bn_fwd_train")
     e = m * c * x.element_size()
-    stats.end("bn_fwd", 3, s, (4 if act == ACT_ADD_RELU else 3) * e + (mask.numel() if mask is not None else 0))
+    stats.end("bn_fwd", 3, s, (4 if act == ACT_ADD_RELU else 3) * e + (mask.numel() - 16 if mask is not None else 0))
     return y, saved, mask
 
 
@@ -281,7 +282,7 @@ def bn_bwd(dy, x, mask, gamma, saved, act, dgamma=None, dbeta=None):
     _check(lib.b200_bn_bwd(_ptr(dy), _ptr(x), _ptr(mask), _ptr(gamma), _ptr(saved), _ptr(dx), _ptr(dz), _ptr(dgamma),
                            _ptr(dbeta), _ptr(ws), ws.numel(), m, c, act, dt, _stream()), "b200_bn_bwd")
     e = m * c * x.element_size()
-    stats.end("bn_bwd", 3, s, (6 if act == ACT_ADD_RELU else 5) * e + (2 * mask.numel() if mask is not None else 0))
+    stats.end("bn_bwd", 3, s, (6 if act == ACT_ADD_RELU else 5) * e + (2 * (mask.numel() - 16) if mask is not None else 0))
     return dx, dz, dgamma, dbeta
 
 

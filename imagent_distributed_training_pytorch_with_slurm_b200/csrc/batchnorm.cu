@@ -32,6 +32,9 @@ int g_bn_vec_bf16 = 8;
 int g_bn_stats_reverse = 1;  // stats/reduce passes walk chunks back to front (tail of the producer's
                              // output is the part most likely still in L2), apply passes front to back
 int g_bn_apply_reverse = 0;
+int g_bn_pipeline = 1;       // 1 = bulk-async (TMA) shared-memory ring kernels where eligible, 0 = direct loads
+int g_bn_pipe_ctas_per_sm = 2;
+int g_bn_pipe_stages = 0;    // 0 = automatic
 
 template <typename T, int VEC>
 struct Unroll {
@@ -69,26 +72,94 @@ Geom make_geom(int64_t m, int c, int vec, int unroll) {
 // Sum `val[0..NV)` over the threads of the CTA that share a channel vector.  On return threads with
 // threadIdx.x < TX hold the CTA totals of their channel vector.
 template <int NV>
-__device__ __forceinline__ void cta_reduce_rows(float (&val)[NV], int tx, float *smem /*[kWarps][32][NV]*/) {
+__device__ __forceinline__ void cta_reduce_rows(float (&val)[NV], int tx, float *smem /*[kThreads][NV]*/) {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (tx <= 32) {
 #pragma unroll
-    for (int k = 0; k < NV; ++k)
-        for (int o = 16; o >= tx; o >>= 1) val[k] += __shfl_xor_sync(0xffffffffu, val[k], o);
-    // with tx < 32 every warp covers all TX channel vectors; with tx == 32 likewise (one row per warp)
-    if (lane < tx) {
+        for (int k = 0; k < NV; ++k)
+            for (int o = 16; o >= tx; o >>= 1) val[k] += __shfl_xor_sync(0xffffffffu, val[k], o);
+        // every warp covers all TX channel vectors: lanes < TX hold the warp's sums
+        if (lane < tx) {
 #pragma unroll
-        for (int k = 0; k < NV; ++k) smem[(warp * 32 + lane) * NV + k] = val[k];
-    }
-    __syncthreads();
-    if (threadIdx.x < tx) {
+            for (int k = 0; k < NV; ++k) smem[(warp * 32 + lane) * NV + k] = val[k];
+        }
+        __syncthreads();
+        if (threadIdx.x < tx) {
 #pragma unroll
-        for (int k = 0; k < NV; ++k) {
-            float s = 0.f;
+            for (int k = 0; k < NV; ++k) {
+                float s = 0.f;
 #pragma unroll
-            for (int w = 0; w < kWarps; ++w) s += smem[(w * 32 + threadIdx.x) * NV + k];
-            val[k] = s;
+                for (int w = 0; w < kWarps; ++w) s += smem[(w * 32 + threadIdx.x) * NV + k];
+                val[k] = s;
+            }
+        }
+    } else {
+        // TX in {64, 128, 256}: threads t, t+TX, ... share a channel vector and sit in different warps
+#pragma unroll
+        for (int k = 0; k < NV; ++k) smem[threadIdx.x * NV + k] = val[k];
+        __syncthreads();
+        if (threadIdx.x < tx) {
+#pragma unroll
+            for (int k = 0; k < NV; ++k) {
+                float s = 0.f;
+                for (int j = threadIdx.x; j < kThreads; j += tx) s += smem[j * NV + k];
+                val[k] = s;
+            }
         }
     }
+}
+
+#include "bn_pipe.cuh"
+
+// Geometry of the bulk-async kernels: every CTA owns whole rows (TX = CV <= 256), tiles of kTileVecs
+// vectors.  The number of chunks is one wave of resident CTAs (148 x g_bn_pipe_ctas_per_sm), capped
+// so that the per-chunk partial sums stay under ~3% of the tensor (never below one CTA per SM); the
+// stage count makes the resident CTAs of an SM keep ~200 KB in flight.
+bool pipe_eligible(int c, int vec, int esize) {
+    if (!g_bn_pipeline || vec * esize != 16) return false;
+    const int cv = c / vec;
+    return cv >= 2 && cv <= kThreads && (cv & (cv - 1)) == 0;
+}
+
+struct PipeGeom {
+    Geom g;
+    int stages;
+    size_t smem;
+};
+
+PipeGeom make_geom_pipe(int64_t m, int c, int vec, int esize, int nt, bool mask, size_t static_smem) {
+    PipeGeom pg;
+    Geom &g = pg.g;
+    g.cv = c / vec;
+    int l = 0;
+    while ((1 << l) < g.cv) ++l;
+    g.txl = l;
+    g.tiles = 1;
+    const int64_t rpt = kTileVecs / g.cv;  // rows per tile
+    const int64_t max_chunks = (m + rpt - 1) / rpt;
+    int64_t want = (int64_t)B200_SM_COUNT * g_bn_pipe_ctas_per_sm;
+    const int64_t by_partial = (int64_t)((double)m * c * esize * 0.03 / ((double)c * 8.0));
+    if (want > by_partial) want = by_partial < B200_SM_COUNT ? B200_SM_COUNT : by_partial;
+    if (want > max_chunks) want = max_chunks;
+    if (want < 1) want = 1;
+    int64_t rpc = (m + want - 1) / want;
+    rpc = (rpc + rpt - 1) / rpt * rpt;
+    g.rpc = rpc;
+    g.nchunk = (int)((m + rpc - 1) / rpc);
+    const int per_sm = (g.nchunk + B200_SM_COUNT - 1) / B200_SM_COUNT;
+    const size_t budget = (size_t)200 * 1024 / per_sm;
+    int st = (int)((budget > static_smem + 128 ? budget - static_smem - 128 : 0) / pipe_stage_bytes(nt, mask));
+    if (st > kMaxStages) st = kMaxStages;
+    if (st < 2) st = 2;
+    if (g_bn_pipe_stages > 0) st = g_bn_pipe_stages;
+    pg.stages = st;
+    pg.smem = pipe_smem_bytes(nt, mask, st);
+    return pg;
+}
+
+template <typename K>
+cudaError_t allow_smem(K kern, size_t bytes) {
+    return cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -416,6 +487,40 @@ int fwd_train_impl(const void *x_, const void *z_, void *y_, uint8_t *mask, cons
     const T *x = static_cast<const T *>(x_);
     const T *z = static_cast<const T *>(z_);
     T *y = static_cast<T *>(y_);
+    if constexpr (VEC * sizeof(T) == 16) if (pipe_eligible(c, VEC, sizeof(T))) {
+        const size_t red_bytes = sizeof(float) * kThreads * 2 * VEC;
+        const PipeGeom ps = make_geom_pipe(m, c, VEC, sizeof(T), 1, false, red_bytes);
+        const Geom &g = ps.g;
+        if (ws_bytes < ws_bytes_for(g, c)) return (int)cudaErrorInvalidValue;
+        const Ws w = carve(ws, g, c);
+        {
+            auto k = bn_stats_pipe_kernel<T, VEC>;
+            cudaError_t e = allow_smem(k, ps.smem);
+            if (e != cudaSuccess) return (int)e;
+            k<<<g.nchunk, kThreads, ps.smem, st>>>(x, w.partial, m, c, g.txl, g.nchunk, g.rpc, g_bn_stats_reverse,
+                                                   ps.stages);
+            B200_CHECK_LAUNCH();
+        }
+        bn_fwd_finalize_kernel<<<(c + kWarps - 1) / kWarps, kThreads, 0, st>>>(w.partial, g.nchunk, g.rpc, m, c, gamma,
+                                                                              beta, rm, rv, nbt, saved, eps, momentum);
+        B200_CHECK_LAUNCH();
+#define B200_APPLY_PIPE(ACT, NT)                                                                                  \
+    do {                                                                                                          \
+        auto k = bn_apply_pipe_kernel<T, VEC, ACT, false>;                                                        \
+        const PipeGeom pa = make_geom_pipe(m, c, VEC, sizeof(T), NT, false, 0);                                   \
+        cudaError_t e = allow_smem(k, pa.smem);                                                                   \
+        if (e != cudaSuccess) return (int)e;                                                                      \
+        k<<<pa.g.nchunk, kThreads, pa.smem, st>>>(x, z, y, mask, saved, nullptr, nullptr, nullptr, nullptr, eps, m, \
+                                                  c, pa.g.txl, pa.g.nchunk, pa.g.rpc, g_bn_apply_reverse,         \
+                                                  pa.stages);                                                     \
+    } while (0)
+        if (act == B200_ACT_NONE) B200_APPLY_PIPE(B200_ACT_NONE, 1);
+        else if (act == B200_ACT_RELU) B200_APPLY_PIPE(B200_ACT_RELU, 1);
+        else B200_APPLY_PIPE(B200_ACT_ADD_RELU, 2);
+#undef B200_APPLY_PIPE
+        B200_CHECK_LAUNCH();
+        return 0;
+    }
     const Geom g = make_geom(m, c, VEC, Unroll<T, VEC>::U);
     if (ws_bytes < ws_bytes_for(g, c)) return (int)cudaErrorInvalidValue;
     const Ws w = carve(ws, g, c);
@@ -443,6 +548,23 @@ int fwd_eval_impl(const void *x_, const void *z_, void *y_, const float *gamma, 
     const T *x = static_cast<const T *>(x_);
     const T *z = static_cast<const T *>(z_);
     T *y = static_cast<T *>(y_);
+    if constexpr (VEC * sizeof(T) == 16) if (pipe_eligible(c, VEC, sizeof(T))) {
+#define B200_APPLY_PIPE(ACT, NT)                                                                                  \
+    do {                                                                                                          \
+        auto k = bn_apply_pipe_kernel<T, VEC, ACT, true>;                                                         \
+        const PipeGeom pa = make_geom_pipe(m, c, VEC, sizeof(T), NT, false, 0);                                   \
+        cudaError_t e = allow_smem(k, pa.smem);                                                                   \
+        if (e != cudaSuccess) return (int)e;                                                                      \
+        k<<<pa.g.nchunk, kThreads, pa.smem, st>>>(x, z, y, nullptr, nullptr, gamma, beta, rm, rv, eps, m, c,      \
+                                                  pa.g.txl, pa.g.nchunk, pa.g.rpc, 0, pa.stages);                 \
+    } while (0)
+        if (act == B200_ACT_NONE) B200_APPLY_PIPE(B200_ACT_NONE, 1);
+        else if (act == B200_ACT_RELU) B200_APPLY_PIPE(B200_ACT_RELU, 1);
+        else B200_APPLY_PIPE(B200_ACT_ADD_RELU, 2);
+#undef B200_APPLY_PIPE
+        B200_CHECK_LAUNCH();
+        return 0;
+    }
     const Geom g = make_geom(m, c, VEC, Unroll<T, VEC>::U);
     const dim3 grid(g.tiles, g.nchunk);
 #define B200_APPLY(ACT)                                                                                      \
@@ -464,6 +586,38 @@ int bwd_impl(const void *dy_, const void *x_, const uint8_t *mask, const float *
     const T *x = static_cast<const T *>(x_);
     T *dx = static_cast<T *>(dx_);
     T *dz = static_cast<T *>(dz_);
+    if constexpr (VEC * sizeof(T) == 16) if (pipe_eligible(c, VEC, sizeof(T))) {
+        if (act == B200_ACT_ADD_RELU && b200_misaligned(mask)) return (int)cudaErrorMisalignedAddress;
+        const size_t red_bytes = sizeof(float) * kThreads * 2 * VEC;
+        const bool masked = act == B200_ACT_ADD_RELU;
+        const PipeGeom pr = make_geom_pipe(m, c, VEC, sizeof(T), 2, masked, red_bytes);
+        const PipeGeom pa = make_geom_pipe(m, c, VEC, sizeof(T), 2, masked, 0);
+        const Geom &g = pr.g;
+        if (ws_bytes < ws_bytes_for(g, c)) return (int)cudaErrorInvalidValue;
+        const Ws w = carve(ws, g, c);
+#define B200_BWD_PIPE(ACT)                                                                                        \
+    do {                                                                                                          \
+        auto kr = bn_bwd_reduce_pipe_kernel<T, VEC, ACT>;                                                         \
+        auto ka = bn_bwd_apply_pipe_kernel<T, VEC, ACT>;                                                          \
+        cudaError_t e = allow_smem(kr, pr.smem);                                                                  \
+        if (e == cudaSuccess) e = allow_smem(ka, pa.smem);                                                        \
+        if (e != cudaSuccess) return (int)e;                                                                      \
+        kr<<<g.nchunk, kThreads, pr.smem, st>>>(dy, x, mask, saved, w.partial, m, c, g.txl, g.nchunk, g.rpc,      \
+                                                g_bn_stats_reverse, pr.stages);                                   \
+        B200_CHECK_LAUNCH();                                                                                      \
+        bn_bwd_finalize_kernel<<<(c + kWarps - 1) / kWarps, kThreads, 0, st>>>(w.partial, g.nchunk, m, c, gamma,   \
+                                                                              saved, dgamma, dbeta, w.coef);     \
+        B200_CHECK_LAUNCH();                                                                                      \
+        ka<<<pa.g.nchunk, kThreads, pa.smem, st>>>(dy, x, mask, saved, w.coef, dx, dz, m, c, pa.g.txl,            \
+                                                   pa.g.nchunk, pa.g.rpc, g_bn_apply_reverse, pa.stages);         \
+        B200_CHECK_LAUNCH();                                                                                      \
+    } while (0)
+        if (act == B200_ACT_NONE) B200_BWD_PIPE(B200_ACT_NONE);
+        else if (act == B200_ACT_RELU) B200_BWD_PIPE(B200_ACT_RELU);
+        else B200_BWD_PIPE(B200_ACT_ADD_RELU);
+#undef B200_BWD_PIPE
+        return 0;
+    }
     const Geom g = make_geom(m, c, VEC, Unroll<T, VEC>::U);
     if (ws_bytes < ws_bytes_for(g, c)) return (int)cudaErrorInvalidValue;
     const Ws w = carve(ws, g, c);
@@ -507,6 +661,9 @@ extern "C" int b200_tune_set(const char *key, int value) {
     if (eq("bn_vec_bf16")) { if (value != 4 && value != 8) return (int)cudaErrorInvalidValue; g_bn_vec_bf16 = value; return 0; }
     if (eq("bn_stats_reverse")) { g_bn_stats_reverse = value != 0; return 0; }
     if (eq("bn_apply_reverse")) { g_bn_apply_reverse = value != 0; return 0; }
+    if (eq("bn_pipeline")) { g_bn_pipeline = value != 0; return 0; }
+    if (eq("bn_pipe_stages")) { if (value < 0 || value > kMaxStages || value == 1) return (int)cudaErrorInvalidValue; g_bn_pipe_stages = value; return 0; }
+    if (eq("bn_pipe_ctas_per_sm")) { if (value < 1 || value > 8) return (int)cudaErrorInvalidValue; g_bn_pipe_ctas_per_sm = value; return 0; }
     return (int)cudaErrorInvalidValue;
 }
 
@@ -523,6 +680,15 @@ extern "C" size_t b200_bn_workspace_bytes(int64_t m, int c, int dtype) {
         const Geom g = make_geom(m, c, vec, unroll);
         const size_t b = ws_bytes_for(g, c);
         if (b > best) best = b;
+        const int cv = c / vec;
+        if (cv >= 2 && cv <= kThreads && (cv & (cv - 1)) == 0) {
+            const int saved_ctas = g_bn_pipe_ctas_per_sm;
+            g_bn_pipe_ctas_per_sm = 8;  // bound over any tuning
+            const PipeGeom gp = make_geom_pipe(m, c, vec, dtype == B200_BF16 ? 2 : 4, 1, false, 0);
+            g_bn_pipe_ctas_per_sm = saved_ctas;
+            const size_t bp = ws_bytes_for(gp.g, c);
+            if (bp > best) best = bp;
+        }
     }
     return best;
 }

@@ -43,6 +43,10 @@ const char *b200_error_string(int code);
  *                      backward of one layer must run under the same value (it fixes the mask layout)
  *   "bn_stats_reverse" 1 = statistics/reduce passes walk the rows back to front (default 1)
  *   "bn_apply_reverse" 1 = apply passes walk the rows back to front (default 0)
+ *   "bn_pipeline"      1 = bulk-async (cp.async.bulk + mbarrier) shared-memory ring kernels where the
+ *                      shape allows (16-byte vectors, power-of-two C/vec), 0 = direct-load kernels
+ *   "bn_pipe_ctas_per_sm" resident CTAs per SM the bulk-async grid is sized for (default 2)
+ *   "bn_pipe_stages"   shared-memory ring depth of the bulk-async kernels, 2..8 (default 0 = automatic)
  * Returns cudaErrorInvalidValue for an unknown key or value. */
 int b200_tune_set(const char *key, int value);
 
@@ -99,7 +103,9 @@ int b200_ce_bwd(const void *logits, const int64_t *target, const float *row_lse,
  * forward, training:  three launches (per-chunk shifted sums -> per-channel finalize -> apply).
  *   saved: float[4*C] out = {mean, invstd, scale = gamma*invstd, shift = beta - mean*scale}
  *   mask : B200_ACT_ADD_RELU only, out, M*C/vec bytes (one byte per `vec` channels, bit k set iff
- *          the pre-activation of channel k of the group is > 0); vec = b200_bn_vec(dtype)
+ *          the pre-activation of channel k of the group is > 0); vec = b200_bn_vec(dtype).  The
+ *          buffer must be 16-byte aligned and 16 bytes longer than that (the backward fetches it
+ *          with 16-byte bulk copies)
  *   z    : B200_ACT_ADD_RELU only.  x,z,y: [M,C] of `dtype`.  Requires M >= 2, C % vec == 0.
  */
 int b200_bn_vec(int dtype);

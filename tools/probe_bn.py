@@ -31,9 +31,8 @@ def timeit(fn, reps=5):
 
 
 def main():
-    knobs = list(itertools.product([8, 4], [592, 1184, 2368], [1, 0]))
-    if len(sys.argv) > 1 and sys.argv[1] == "quick":
-        knobs = [(8, 1184, 1)]
+    # (vec, direct-kernel CTAs, reverse, pipeline, pipeline CTAs/SM)
+    knobs = [(8, 1184, 1, 0, 3), (8, 1184, 1, 1, 1), (8, 1184, 1, 1, 2), (8, 1184, 1, 1, 3)]
     res = []
     for shape in SHAPES:
         n, c, h, w = shape
@@ -43,11 +42,13 @@ def main():
         g, b = torch.ones(c, device=dev), torch.zeros(c, device=dev)
         rm, rv = torch.zeros(c, device=dev), torch.ones(c, device=dev)
         e = x.numel() * 2
-        for vec, ctas, rev in knobs:
+        for vec, ctas, rev, pipe, pctas in knobs:
             cabi.tune_set("bn_vec_bf16", vec)
             cabi.tune_set("bn_target_ctas", ctas)
             cabi.tune_set("bn_stats_reverse", rev)
-            row = {"shape": shape, "vec": vec, "ctas": ctas, "rev": rev}
+            cabi.tune_set("bn_pipeline", pipe)
+            cabi.tune_set("bn_pipe_ctas_per_sm", pctas)
+            row = {"shape": shape, "vec": vec, "ctas": ctas, "rev": rev, "pipe": pipe, "pctas": pctas}
             for act, name in ((1, "relu"), (2, "add_relu")):
                 zz = z if act == 2 else None
                 _, saved, mask = cabi.bn_fwd_train(x, zz, g, b, rm, rv, None, 1e-5, 0.1, act)
