@@ -170,7 +170,7 @@ def run_ours(a):
 
     def step(i):
         boxes, flips, tgt = params[i]
-        x = _cabi.input_stage(images, boxes, flips, a.image, a.image, mean, std, dtype)
+        x = _cabi.input_stage(images, boxes, flips, a.image, a.image, mean, std, dtype, _cabi.LAYOUT_S2D_STEM)
         logits = model(x)
         loss = crit(logits, tgt)
         opt.zero_grad()
@@ -212,10 +212,10 @@ def run_ours(a):
     if not a.no_e2e:
         wl = b200.SyntheticImageNet(a.batch, max(a.warmup, 1), a.src, a.image, rank=rank, dtype=dtype, host=True)
         tl = b200.SyntheticImageNet(a.batch, a.steps, a.src, a.image, rank=rank, dtype=dtype, host=True)
-        b200.train(wl, model, crit, opt, 0, world, sync_every=1)
+        b200.train(wl, model, crit, opt, 0, world, sync_every=1, lag=1)
         barrier()
         t0 = time.perf_counter()
-        b200.train(tl, model, crit, opt, 0, world, sync_every=1)  # every step: H2D of the batch, D2H of the loss
+        b200.train(tl, model, crit, opt, 0, world, sync_every=1, lag=1)  # every step: H2D of the batch, D2H of a loss
         barrier()
         dt = torch.tensor([time.perf_counter() - t0], device=dev)
         if world > 1:

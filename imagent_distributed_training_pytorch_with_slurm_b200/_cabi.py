@@ -15,7 +15,7 @@ LIB_PATH = os.path.join(_HERE, "libb200_imagenet.so")
 
 F32, BF16 = 0, 1
 ACT_NONE, ACT_RELU, ACT_ADD_RELU = 0, 1, 2
-LAYOUT_NHWC, LAYOUT_NCHW = 0, 1
+LAYOUT_NHWC, LAYOUT_NCHW, LAYOUT_S2D_STEM = 0, 1, 2
 ABI_VERSION = 1
 
 _c = ctypes
@@ -36,6 +36,8 @@ SIGNATURES = {
                                  _i32, _i32, _vp]),
     "b200_bn_fwd_eval": (_i32, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _i64, _i32, _f32, _i32, _i32, _vp]),
     "b200_bn_bwd": (_i32, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _sz, _i64, _i32, _i32, _i32, _vp]),
+    "b200_maxpool3x3s2_fwd": (_i32, [_vp, _vp, _vp, _i64, _i32, _i32, _i32, _i32, _vp]),
+    "b200_maxpool3x3s2_bwd": (_i32, [_vp, _vp, _vp, _i64, _i32, _i32, _i32, _i32, _vp]),
     "b200_input_workspace_bytes": (_sz, [_i64, _i32, _i32, _i32, _i32]),
     "b200_input_crop_resize_flip_norm": (_i32, [_vp, _vp, _vp, _vp, _vp, _sz, _i64, _i32, _i32, _i32, _i32,
                                                 _c.POINTER(_f32), _c.POINTER(_f32), _i32, _i32, _vp]),
@@ -286,11 +288,42 @@ def bn_bwd(dy, x, mask, gamma, saved, act, dgamma=None, dbeta=None):
     return dx, dz, dgamma, dbeta
 
 
+# ---- K6 -------------------------------------------------------------------------------------------
+def maxpool_fwd(x):
+    """3x3/2/1 max-pool of a channels-last activation.  Returns (y, argmax uint8 [N,OH,OW,C])."""
+    _need_cuda(x)
+    if x.dim() != 4 or not x.is_contiguous(memory_format=torch.channels_last):
+        raise B200Error("max-pool kernel needs a channels-last 4-d activation")
+    n, c, h, w = x.shape
+    oh, ow = (h - 1) // 2 + 1, (w - 1) // 2 + 1
+    y = torch.empty((n, c, oh, ow), dtype=x.dtype, device=x.device, memory_format=torch.channels_last)
+    arg = torch.empty((n, oh, ow, c), dtype=torch.uint8, device=x.device)
+    s = stats.begin("maxpool_fwd")
+    _check(load().b200_maxpool3x3s2_fwd(_ptr(x), _ptr(y), _ptr(arg), n, c, h, w, dtype_code(x), _stream()),
+           "b200_maxpool3x3s2_fwd")
+    stats.end("maxpool_fwd", 1, s, x.numel() * x.element_size() + y.numel() * (x.element_size() + 1))
+    return y, arg
+
+
+def maxpool_bwd(dy, arg, in_shape):
+    _need_cuda(dy, arg)
+    n, c, h, w = in_shape
+    if not dy.is_contiguous(memory_format=torch.channels_last):
+        raise B200Error("max-pool kernel needs a channels-last gradient")
+    dx = torch.empty((n, c, h, w), dtype=dy.dtype, device=dy.device, memory_format=torch.channels_last)
+    s = stats.begin("maxpool_bwd")
+    _check(load().b200_maxpool3x3s2_bwd(_ptr(dy), _ptr(arg), _ptr(dx), n, c, h, w, dtype_code(dy), _stream()),
+           "b200_maxpool3x3s2_bwd")
+    stats.end("maxpool_bwd", 1, s, dx.numel() * dx.element_size() + dy.numel() * (dy.element_size() + 1))
+    return dx
+
+
 # ---- K1 -------------------------------------------------------------------------------------------
 def input_stage(images, boxes, flips, out_h, out_w, mean, std, out_dtype=torch.bfloat16, layout=LAYOUT_NHWC):
     """images uint8 [N,Hs,Ws,3] (device), boxes int32 [N,4] (device), flips uint8 [N] (device) or
     None.  Returns [N,3,out_h,out_w] logical NCHW: channels-last strides for LAYOUT_NHWC,
-    contiguous for LAYOUT_NCHW."""
+    contiguous for LAYOUT_NCHW; for LAYOUT_S2D_STEM a channels-last [N,16,(out_h+6)/2,(out_w+6)/2]
+    tensor tagged ``_b200_s2d_stem`` (see include/b200_imagenet.h)."""
     _need_cuda(images, boxes, flips)
     assert images.dtype == torch.uint8 and images.dim() == 4 and images.shape[3] == 3 and images.is_contiguous()
     assert boxes.dtype == torch.int32 and boxes.is_contiguous() and boxes.shape == (images.shape[0], 4)
@@ -301,6 +334,12 @@ def input_stage(images, boxes, flips, out_h, out_w, mean, std, out_dtype=torch.b
     if layout == LAYOUT_NHWC:
         out = torch.empty((n, 3, out_h, out_w), dtype=out_dtype, device=images.device,
                           memory_format=torch.channels_last)
+    elif layout == LAYOUT_S2D_STEM:
+        if out_h % 2 or out_w % 2:
+            raise B200Error("the space-to-depth stem layout needs even output sizes")
+        out = torch.empty((n, 16, (out_h + 6) // 2, (out_w + 6) // 2), dtype=out_dtype, device=images.device,
+                          memory_format=torch.channels_last)
+        out._b200_s2d_stem = (out_h, out_w)  # tells B200ResNet to run the rearranged stem convolution
     else:
         out = torch.empty((n, 3, out_h, out_w), dtype=out_dtype, device=images.device)
     nbytes = lib.b200_input_workspace_bytes(n, sh, sw, out_h, out_w)

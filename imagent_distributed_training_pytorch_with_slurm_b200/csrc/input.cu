@@ -169,6 +169,15 @@ input_resample_kernel(const uint8_t *__restrict__ images, const int32_t *__restr
             o[0] = cast_out<OutT>(f0);
             o[1] = cast_out<OutT>(f1);
             o[2] = cast_out<OutT>(f2);
+        } else if (layout == B200_LAYOUT_S2D_STEM) {
+            // image zero-padded by 3, then 2x2 space-to-depth: pixel (py,px) -> cell (py/2,px/2),
+            // channels (py%2*2 + px%2)*3 + ch of a 16-channel cell (12 used, 4 stay zero)
+            const int py = yy + 3, px = xd + 3;
+            const int sy = (out_h + 6) >> 1, sx = (out_w + 6) >> 1;
+            OutT *o = out + ((((int64_t)s * sy + (py >> 1)) * sx + (px >> 1)) << 4) + ((py & 1) * 2 + (px & 1)) * 3;
+            o[0] = cast_out<OutT>(f0);
+            o[1] = cast_out<OutT>(f1);
+            o[2] = cast_out<OutT>(f2);
         } else {
             const int64_t plane = (int64_t)out_h * out_w;
             OutT *o = out + (int64_t)s * 3 * plane + (int64_t)yy * out_w + xd;
@@ -200,7 +209,9 @@ extern "C" int b200_input_crop_resize_flip_norm(const uint8_t *images, const int
     if (!images || !boxes || !out || !workspace || !mean3 || !std3) return (int)cudaErrorInvalidValue;
     if (n < 1 || src_h < 1 || src_w < 1 || out_h < 1 || out_w < 1) return (int)cudaErrorInvalidValue;
     if (out_dtype != B200_F32 && out_dtype != B200_BF16) return (int)cudaErrorInvalidValue;
-    if (out_layout != B200_LAYOUT_NHWC && out_layout != B200_LAYOUT_NCHW) return (int)cudaErrorInvalidValue;
+    if (out_layout != B200_LAYOUT_NHWC && out_layout != B200_LAYOUT_NCHW && out_layout != B200_LAYOUT_S2D_STEM)
+        return (int)cudaErrorInvalidValue;
+    if (out_layout == B200_LAYOUT_S2D_STEM && ((out_h | out_w) & 1)) return (int)cudaErrorInvalidValue;
     if ((int64_t)src_h > 8 * (int64_t)out_h || (int64_t)src_w > 8 * (int64_t)out_w) return (int)cudaErrorInvalidValue;
     if (n > 65535) return (int)cudaErrorInvalidValue;
     if (workspace_bytes < b200_input_workspace_bytes(n, src_h, src_w, out_h, out_w)) return (int)cudaErrorInvalidValue;
@@ -212,6 +223,11 @@ extern "C" int b200_input_crop_resize_flip_norm(const uint8_t *images, const int
     input_coeff_kernel<<<(unsigned)((items + kThreads - 1) / kThreads), kThreads, 0, st>>>(boxes, n, out_h, out_w, KX,
                                                                                            KY, ws);
     B200_CHECK_LAUNCH();
+    if (out_layout == B200_LAYOUT_S2D_STEM) {  // border cells and the 4 spare channels must read as zero
+        const size_t bytes = (size_t)n * ((out_h + 6) / 2) * ((out_w + 6) / 2) * 16 * (out_dtype == B200_F32 ? 4 : 2);
+        cudaError_t e = cudaMemsetAsync(out, 0, bytes, st);
+        if (e != cudaSuccess) return (int)e;
+    }
     const int max_rows = max_src_rows_for(src_h, out_h);
     const size_t smem = 3 * 256 * sizeof(float) + (size_t)max_rows * out_w * 3;
     if (smem > 200 * 1024) return (int)cudaErrorInvalidValue;

@@ -73,9 +73,11 @@ def draw_batch_params(n, height, width, generator=None, random_crop=True, flip_p
 
 
 class DeviceInputStage:
-    """uint8 NHWC host (pinned) or device batch -> normalised channels-last activation on the GPU."""
+    """uint8 NHWC host (pinned) or device batch -> normalised channels-last activation on the GPU.
+    The default output layout is the space-to-depth form B200ResNet's stem consumes directly
+    (``_cabi.LAYOUT_S2D_STEM``); pass ``layout=_cabi.LAYOUT_NHWC`` for a plain [N,3,H,W] tensor."""
 
-    def __init__(self, out_size, mean, std, dtype=torch.bfloat16, device=None, layout=_cabi.LAYOUT_NHWC):
+    def __init__(self, out_size, mean, std, dtype=torch.bfloat16, device=None, layout=_cabi.LAYOUT_S2D_STEM):
         self.out_h, self.out_w = (out_size, out_size) if isinstance(out_size, int) else out_size
         self.mean, self.std, self.dtype, self.layout = tuple(mean), tuple(std), dtype, layout
         self.device = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)

@@ -13,7 +13,9 @@ What changes underneath (the observable results do not):
     epoch averages are bit-identical to per-iteration logging;
   * ``batch_time.sum`` (the "Train time" the reference prints, imagenet.py:403) is a telescoping sum
     of wall-clock deltas, so it only needs the final synchronisation to be the same number.
-``sync_every=1`` restores the reference's per-iteration synchronisation exactly.
+``sync_every=1`` restores the reference's per-iteration synchronisation exactly; ``sync_every=1, lag=1``
+still reads every iteration's result on the host, one iteration late, so the device never waits for
+the host.
 """
 import time
 
@@ -70,27 +72,67 @@ def _triple(criterion, loss, logits, target):
     return torch.stack([loss.data.float().reshape(()), p1[0], p5[0]])
 
 
-def _drain(pending, world_size, weight, meters):
-    if not pending:
-        return
-    m = reduce_tensor(torch.stack(pending), world_size)
-    rows = m.cpu().tolist()  # the host sync
-    for lo, p1, p5 in rows:
-        meters[0].update(lo, weight)
-        meters[1].update(p1, weight)
-        meters[2].update(p5, weight)
-    pending.clear()
+class _MetricLog:
+    """Per-iteration {loss, top-1, top-5} triples -> host meters.
+
+    Triples are grouped (``sync_every`` iterations per group, one group per epoch when None); a
+    finished group is stacked, all-reduced once, divided by the world size in float32 and copied to
+    pinned host memory asynchronously, followed by an event.  The host waits only for the event of the
+    group that finished ``lag`` groups earlier, so with ``lag >= 1`` the GPU never idles waiting for
+    Python to read a scalar; the meters still receive every value, in order."""
+
+    def __init__(self, world_size, meters, sync_every, lag):
+        self.world_size, self.meters = world_size, meters
+        self.sync_every, self.lag = sync_every, max(0, int(lag))
+        self.pending, self.inflight, self.weight = [], [], 1
+
+    def add(self, triple, weight):
+        self.pending.append(triple)
+        self.weight = weight
+        if self.sync_every and len(self.pending) >= self.sync_every:
+            self._launch()
+            self._collect(self.lag)
+            return True
+        return False
+
+    def _launch(self):
+        if not self.pending:
+            return
+        m = reduce_tensor(torch.stack(self.pending), self.world_size)
+        self.pending = []
+        if m.is_cuda:
+            host = torch.empty(m.shape, dtype=m.dtype, pin_memory=True)
+            host.copy_(m, non_blocking=True)
+            ev = torch.cuda.Event()
+            ev.record()
+        else:
+            host, ev = m, None
+        self.inflight.append((host, ev, self.weight))
+
+    def _collect(self, keep):
+        while len(self.inflight) > keep:
+            host, ev, weight = self.inflight.pop(0)
+            if ev is not None:
+                ev.synchronize()  # the host sync
+            for lo, p1, p5 in host.tolist():
+                self.meters[0].update(lo, weight)
+                self.meters[1].update(p1, weight)
+                self.meters[2].update(p5, weight)
+
+    def finish(self):
+        self._launch()
+        self._collect(0)
 
 
 def _to_device(t):
     return t if t.is_cuda else t.cuda(non_blocking=True)
 
 
-def train(train_loader, model, criterion, optimizer, epoch, world_size, sync_every=None):
+def train(train_loader, model, criterion, optimizer, epoch, world_size, sync_every=None, lag=0):
     batch_time, data_time = AverageMeter(), AverageMeter()
     losses, top1, top5 = AverageMeter(), AverageMeter(), AverageMeter()
     model.train()
-    pending, weight, iters = [], 1, 0
+    log, iters = _MetricLog(world_size, (losses, top1, top5), sync_every, lag), 0
     start = end = time.time()
     for i, (input, target) in enumerate(train_loader):
         data_time.update(time.time() - end)
@@ -103,15 +145,13 @@ def train(train_loader, model, criterion, optimizer, epoch, world_size, sync_eve
         loss.backward()
         optimizer.step()
 
-        pending.append(_triple(criterion, loss, logits, target))
-        weight = input[0].size(0)
         iters += 1
-        if sync_every and iters % sync_every == 0:
-            _drain(pending, world_size, weight, (losses, top1, top5))
-            torch.cuda.synchronize()
+        if log.add(_triple(criterion, loss, logits, target), input[0].size(0)):
+            if lag == 0:
+                torch.cuda.synchronize()  # imagenet.py:147
             batch_time.update(time.time() - end)
         end = time.time()
-    _drain(pending, world_size, weight, (losses, top1, top5))
+    log.finish()
     torch.cuda.synchronize()
     total = time.time() - start
     if batch_time.count < iters:  # spread the un-attributed wall time evenly; the sum is what is reported
@@ -122,26 +162,24 @@ def train(train_loader, model, criterion, optimizer, epoch, world_size, sync_eve
     return losses.avg, top1.avg, top5.avg, batch_time.sum
 
 
-def validate(val_loader, model, criterion, world_size, sync_every=None):
+def validate(val_loader, model, criterion, world_size, sync_every=None, lag=0):
     batch_time = AverageMeter()
     losses, top1, top5 = AverageMeter(), AverageMeter(), AverageMeter()
     model.eval()
-    pending, weight, iters = [], 1, 0
+    log, iters = _MetricLog(world_size, (losses, top1, top5), sync_every, lag), 0
     with torch.no_grad():
         start = end = time.time()
         for i, (input, target) in enumerate(val_loader):
             input, target = _to_device(input), _to_device(target)
             logits = model(input)
             loss = criterion(logits, target)
-            pending.append(_triple(criterion, loss, logits, target))
-            weight = input[0].size(0)
             iters += 1
-            if sync_every and iters % sync_every == 0:
-                _drain(pending, world_size, weight, (losses, top1, top5))
-                torch.cuda.synchronize()
+            if log.add(_triple(criterion, loss, logits, target), input[0].size(0)):
+                if lag == 0:
+                    torch.cuda.synchronize()
                 batch_time.update(time.time() - end)
             end = time.time()
-        _drain(pending, world_size, weight, (losses, top1, top5))
+        log.finish()
         torch.cuda.synchronize()
         total = time.time() - start
     if batch_time.count < iters:

@@ -80,6 +80,41 @@ class _Conv(nn.Module):
         return gx
 
 
+class _StemS2D:
+    """The stem convolution (7x7, stride 2, padding 3, 3->64; torchvision resnet.py:197) on an input
+    that the input kernel already delivered zero-padded and 2x2 space-to-depth'ed ([N,16,H/2+3,W/2+3]):
+    with the weights rearranged the same way it is a 4x4, stride-1, unpadded convolution over 16
+    channels - identical sums, ~2.3x faster in cuDNN than the 3-channel strided form (measured
+    1.60+0.91 ms -> 0.52+0.59 ms fwd+wgrad at N=256).  The rearranged weights are rebuilt from the
+    (shadow) parameter once per optimizer step; the weight gradient is mapped back to [64,3,7,7]."""
+
+    def __init__(self, conv, arena):
+        if (conv.weight.shape[1:] != (3, 7, 7) or tuple(conv.stride) != (2, 2) or tuple(conv.padding) != (3, 3)
+                or tuple(conv.dilation) != (1, 1) or conv.groups != 1):
+            raise ValueError("space-to-depth stem needs the torchvision 7x7/2/3 RGB stem")
+        self.conv, self.arena, self._w, self._at = conv, arena, None, -1
+
+    def weight(self):
+        if self._at != self.arena.steps or self._w is None:
+            w7 = self.conv.w_compute
+            k = w7.shape[0]
+            w8 = torch.nn.functional.pad(w7, (0, 1, 0, 1))                       # [K,3,8,8]
+            w = w8.reshape(k, 3, 4, 2, 4, 2).permute(0, 3, 5, 1, 2, 4)           # K, dy, dx, ch, R, S
+            w = torch.nn.functional.pad(w.reshape(k, 12, 4, 4), (0, 0, 0, 0, 0, 4))
+            self._w, self._at = w.contiguous(memory_format=torch.channels_last), self.arena.steps
+        return self._w
+
+    def fwd(self, x):
+        return torch.ops.aten.convolution(x, self.weight(), None, (1, 1), (0, 0), (1, 1), False, (0, 0), 1)
+
+    def bwd(self, gy, x):
+        _, gw, _ = torch.ops.aten.convolution_backward(gy, x, self.weight(), None, (1, 1), (0, 0), (1, 1), False,
+                                                       (0, 0), 1, (False, True, False))
+        k = gw.shape[0]
+        g = gw[:, :12].reshape(k, 2, 2, 3, 4, 4).permute(0, 3, 4, 1, 5, 2).reshape(k, 3, 8, 8)
+        self.conv.grad_view.copy_(g[:, :, :7, :7])
+
+
 class _BN(nn.Module):
     def __init__(self, tv):
         super().__init__()
@@ -223,11 +258,13 @@ class B200ResNet(nn.Module):
         self.arch, self.act_dtype, self.device = arch, dtype, device
 
         self.conv1, self.bn1 = _Conv(tv.conv1), _BN(tv.bn1)
-        self.pool = (tv.maxpool.kernel_size, tv.maxpool.stride, tv.maxpool.padding)
+        if (tv.maxpool.kernel_size, tv.maxpool.stride, tv.maxpool.padding) != (3, 2, 1):
+            raise ValueError("only the torchvision stem max-pool (3x3, stride 2, padding 1) is implemented")
         for li in range(1, 5):
             setattr(self, f"layer{li}", nn.Sequential(*[_Block(b) for b in getattr(tv, f"layer{li}")]))
         self.fc = _Linear(tv.fc)
         self._adopt(tv)
+        self.__dict__["_stem_s2d"] = None
         self._anchor = torch.zeros((), device=device, requires_grad=True)
         self.__dict__["_sink"] = None  # data-parallel wrapper (grad_ready / backward_done); not a submodule
         self.grad_predivide = 1.0  # 1/world_size, set by the wrapper (DDP's pre-division)
@@ -300,7 +337,18 @@ class B200ResNet(nn.Module):
         self.__dict__["_sink"] = sink  # bypass nn.Module registration (the wrapper owns us, not vice versa)
 
     # ---- execution ------------------------------------------------------------------------------
+    def _stem(self, x):
+        """(convolution object, input) for the stem: the space-to-depth form when the input kernel
+        delivered that layout, the plain 7x7/2 convolution otherwise."""
+        if getattr(x, "_b200_s2d_stem", None) is not None:
+            if self._stem_s2d is None:
+                self.__dict__["_stem_s2d"] = _StemS2D(self.conv1, self.arena)
+            return self._stem_s2d
+        return self.conv1
+
     def _prep_input(self, x):
+        if getattr(x, "_b200_s2d_stem", None) is not None and x.dtype == self.act_dtype and x.device == self.device:
+            return x
         if x.device != self.device:
             raise _cabi.B200Error("input must already be on the model's CUDA device")
         if x.dtype != self.act_dtype or not x.is_contiguous(memory_format=torch.channels_last):
@@ -316,13 +364,14 @@ class B200ResNet(nn.Module):
         return self._forward_eval(x)
 
     def _forward_train(self, x):
-        tape = {"x0": x}
-        t = self.conv1.fwd(x)
+        stem = self._stem(x)
+        tape = {"x0": x, "stem": stem}
+        t = stem.fwd(x)
         a, saved, _ = self.bn1.fwd_train(t, _cabi.ACT_RELU)
-        tape["t1"], tape["saved1"], tape["a1"] = t, saved, a
-        k, s, p = self.pool
-        cur, idx = torch.ops.aten.max_pool2d_with_indices(a, [k, k], [s, s], [p, p], [1, 1], False)
-        tape["pool_idx"] = idx
+        tape["t1"], tape["saved1"] = t, saved
+        cur, idx = _cabi.maxpool_fwd(a)
+        tape["pool_idx"], tape["pool_in_shape"] = idx, a.shape
+        del a
         tape["blocks"] = []
         for li in range(1, 5):
             for blk in getattr(self, f"layer{li}"):
@@ -335,9 +384,8 @@ class B200ResNet(nn.Module):
         return logits, tape
 
     def _forward_eval(self, x):
-        a = self.bn1.fwd_eval(self.conv1.fwd(x), _cabi.ACT_RELU)
-        k, s, p = self.pool
-        cur = torch.ops.aten.max_pool2d(a, [k, k], [s, s], [p, p], [1, 1], False)
+        a = self.bn1.fwd_eval(self._stem(x).fwd(x), _cabi.ACT_RELU)
+        cur, _ = _cabi.maxpool_fwd(a)
         for li in range(1, 5):
             for blk in getattr(self, f"layer{li}"):
                 cur = blk.fwd_eval(cur)
@@ -371,13 +419,13 @@ class B200ResNet(nn.Module):
                 g = layer[bi].bwd(g, blocks.pop())
                 if sink is not None:
                     sink.grad_ready(self._marks[(li, bi)])
-        k, s, p = self.pool
-        a1 = tape.pop("a1")
-        g = torch.ops.aten.max_pool2d_with_indices_backward(g, a1, [k, k], [s, s], [p, p], [1, 1], False,
-                                                            tape.pop("pool_idx"))
-        del a1
+        g = _cabi.maxpool_bwd(g, tape.pop("pool_idx"), tape.pop("pool_in_shape"))
         g, _ = self.bn1.bwd(g, tape.pop("t1"), tape.pop("saved1"), None, _cabi.ACT_RELU)
-        self.conv1.bwd(g, tape.pop("x0"), need_gx=False)
+        stem = tape.pop("stem")
+        if stem is self.conv1:
+            stem.bwd(g, tape.pop("x0"), need_gx=False)
+        else:
+            stem.bwd(g, tape.pop("x0"))
         if sink is not None:
             sink.grad_ready(0)
             sink.backward_done()

@@ -31,7 +31,7 @@ extern "C" {
 
 enum { B200_F32 = 0, B200_BF16 = 1 };
 enum { B200_ACT_NONE = 0, B200_ACT_RELU = 1, B200_ACT_ADD_RELU = 2 };
-enum { B200_LAYOUT_NHWC = 0, B200_LAYOUT_NCHW = 1 };
+enum { B200_LAYOUT_NHWC = 0, B200_LAYOUT_NCHW = 1, B200_LAYOUT_S2D_STEM = 2 };
 
 /* Library identity / diagnostics. */
 int b200_abi_version(void);
@@ -146,7 +146,12 @@ int b200_bn_bwd(const void *dy, const void *x, const uint8_t *mask, const float 
  *   images : uint8 [n, src_h, src_w, 3]
  *   boxes  : int32 [n,4] rows (top, left, height, width), inside the image, on the DEVICE
  *   flips  : uint8 [n] (non-zero = mirror), on the DEVICE
- *   out    : [n,out_h,out_w,3] (B200_LAYOUT_NHWC) or [n,3,out_h,out_w] (B200_LAYOUT_NCHW)
+ *   out    : [n,out_h,out_w,3] (B200_LAYOUT_NHWC), [n,3,out_h,out_w] (B200_LAYOUT_NCHW), or
+ *            [n,(out_h+6)/2,(out_w+6)/2,16] (B200_LAYOUT_S2D_STEM: the image zero-padded by 3 pixels and
+ *            2x2 space-to-depth'ed, cell channel (py%2*2+px%2)*3+ch, 4 spare channels zero; out_h and
+ *            out_w even).  With the 7x7 weights rearranged the same way, the stem convolution
+ *            (7x7, stride 2, padding 3, 3->64; torchvision resnet.py:197) becomes a 4x4 stride-1
+ *            convolution over 16 channels - the same sums, a shape the tensor cores like better
  *   mean3/std3 : HOST pointers to 3 floats each
  * two launches (coefficient tables into workspace, then the resample).  Down-scaling is limited to
  * src/out <= 8 per axis.
@@ -156,6 +161,22 @@ int b200_input_crop_resize_flip_norm(const uint8_t *images, const int32_t *boxes
                                      void *workspace, size_t workspace_bytes, int64_t n, int src_h, int src_w,
                                      int out_h, int out_w, const float *mean3, const float *std3, int out_dtype,
                                      int out_layout, void *stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * K6  3x3 / stride 2 / pad 1 max-pooling, channels-last, forward and backward.
+ * Replaces nn.MaxPool2d(kernel_size=3, stride=2, padding=1) after the stem (torchvision
+ * resnet.py:200,270) and its gradient inside loss.backward() (imagenet.py:128), i.e. ATen's
+ * max_pool2d_with_indices / max_pool2d_with_indices_backward (int64 argmax tensor).
+ *   x      : [n,h,w,c] of dtype, c % 8 == 0        y : [n,oh,ow,c], oh = (h-1)/2+1, ow = (w-1)/2+1
+ *   argmax : uint8 [n,oh,ow,c]: position 0..8 (row-major inside the window) of the maximum; the first
+ *            maximum wins, NaN counts as maximum (ATen's rule)
+ *   backward: dx[n,h,w,c] = sum of dy over the (at most 4) windows whose argmax is that pixel,
+ *            accumulated in float32; every element of dx is written (no zero-fill needed).
+ */
+int b200_maxpool3x3s2_fwd(const void *x, void *y, uint8_t *argmax, int64_t n, int c, int h, int w, int dtype,
+                          void *stream);
+int b200_maxpool3x3s2_bwd(const void *dy, const uint8_t *argmax, void *dx, int64_t n, int c, int h, int w, int dtype,
+                          void *stream);
 
 #ifdef __cplusplus
 }

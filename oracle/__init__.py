@@ -23,6 +23,8 @@ module              reference site it follows
 ``sgd``             ``imagenet.py:325,131`` -> ``torch/optim/sgd.py:343-380``
 ``batchnorm``       ``torchvision/models/resnet.py:93-103,147-161,240-243`` ->
                     ``torch/nn/modules/batchnorm.py:160-206``
+``maxpool``         ``torchvision/models/resnet.py:200,270`` MaxPool2d(3,2,1) and its
+                    gradient (ATen first-maximum tie rule)
 ``cross_entropy``   ``imagenet.py:124,323`` -> ``torch/nn/functional.py:3421-3504``
                     fused with ``accuracy`` (``imagenet.py:63-79``)
 ``train_cpu``       ``imagenet.py:97-151`` train() and ``:166-210`` validate()

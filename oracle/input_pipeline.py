@@ -163,3 +163,17 @@ def flip_draw_oracle(p=0.5, generator=None):
     import torch
 
     return bool(torch.rand(1, generator=generator) < p)
+
+
+def space_to_depth_stem_oracle(x_nhwc):
+    """[N,H,W,3] -> [N,(H+6)/2,(W+6)/2,16]: zero-pad by 3 (the stem convolution's padding, torchvision
+    resnet.py:197), then 2x2 space-to-depth with cell channel (py%2*2 + px%2)*3 + ch; 4 spare channels
+    are zero.  Pure re-indexing of ``input_stage_oracle``'s output."""
+    x = np.asarray(x_nhwc)
+    n, h, w, c = x.shape
+    p = np.zeros((n, h + 6, w + 6, c), dtype=x.dtype)
+    p[:, 3:3 + h, 3:3 + w, :] = x
+    p = p.reshape(n, (h + 6) // 2, 2, (w + 6) // 2, 2, c).transpose(0, 1, 3, 2, 4, 5)  # N, Y, X, dy, dx, ch
+    out = np.zeros((n, (h + 6) // 2, (w + 6) // 2, 16), dtype=x.dtype)
+    out[..., :12] = p.reshape(n, (h + 6) // 2, (w + 6) // 2, 12)
+    return out

@@ -9,6 +9,7 @@ import torch
 from oracle import batchnorm as obn
 from oracle import cross_entropy as oce
 from oracle import input_pipeline as oin
+from oracle import maxpool as omp
 from oracle import sgd as osgd
 
 
@@ -98,4 +99,18 @@ def input_stage(images, boxes, flips, out_h, out_w, mean, std, out_dtype=torch.b
     fl = np.zeros(images.shape[0], dtype=bool) if flips is None else flips.numpy().astype(bool)
     out = oin.input_stage_oracle(images.numpy(), boxes.numpy(), fl, out_h, out_w, mean, std)
     t = torch.from_numpy(out).to(out_dtype).permute(0, 3, 1, 2)  # NHWC memory, NCHW shape
+    if layout == 2:
+        s2d = torch.from_numpy(oin.space_to_depth_stem_oracle(out)).to(out_dtype).permute(0, 3, 1, 2)
+        s2d._b200_s2d_stem = (out_h, out_w)
+        return s2d
     return t if layout == 0 else t.contiguous()
+
+
+def maxpool_fwd(x):
+    y, pos = omp.maxpool3x3s2_fwd_oracle(x.permute(0, 2, 3, 1).float().numpy())
+    return torch.from_numpy(y).to(x.dtype).permute(0, 3, 1, 2), torch.from_numpy(pos)
+
+
+def maxpool_bwd(dy, arg, in_shape):
+    dx = omp.maxpool3x3s2_bwd_oracle(dy.permute(0, 2, 3, 1).float().numpy(), arg.numpy(), (in_shape[2], in_shape[3]))
+    return torch.from_numpy(dx).to(dy.dtype).permute(0, 3, 1, 2)

@@ -26,7 +26,8 @@ def _worker(rank, world, port, gold, q):
         from oracle import train_cpu
         from tests import cpu_kernel_standins as s
 
-        for name in ("bn_fwd_train", "bn_fwd_eval", "bn_bwd", "ce_topk_fwd", "ce_bwd", "sgd_flat", "input_stage"):
+        for name in ("bn_fwd_train", "bn_fwd_eval", "bn_bwd", "ce_topk_fwd", "ce_bwd", "sgd_flat", "input_stage", "maxpool_fwd",
+                 "maxpool_bwd"):
             setattr(cabi, name, getattr(s, name))
         eng._to_device = lambda t: t
         torch.cuda.synchronize = lambda *a, **k: None
@@ -38,15 +39,6 @@ def _worker(rank, world, port, gold, q):
         opt = b200.FlatSGD(model.parameters(), gold["lr"], momentum=0.9, weight_decay=1e-4)
         batches = train_cpu.synthetic_batches(rank, gold["steps"], gold["batch_per_rank"], gold["image"], 1000,
                                               seed=gold["data_seed"])
-        trace = []
-        orig = eng._drain
-
-        def spy(pending, world_size, weight, meters):
-            n0 = meters[0].count
-            orig(pending, world_size, weight, meters)
-            trace.append((meters[0].sum, meters[1].sum, meters[2].sum, meters[0].count - n0))
-
-        eng._drain = spy
         res = b200.train(batches, model, crit, opt, 0, world, sync_every=1)
         sd = model.state_dict()
         out = {"rank": rank, "epoch": [float(v) for v in res[:3]], "n_buckets": len(model.buckets),

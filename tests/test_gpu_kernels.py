@@ -12,6 +12,7 @@ import torch
 from oracle import batchnorm as obn
 from oracle import cross_entropy as oce
 from oracle import input_pipeline as oin
+from oracle import maxpool as omp
 from oracle import sgd as osgd
 
 import imagent_distributed_training_pytorch_with_slurm_b200._cabi as cabi
@@ -327,3 +328,57 @@ def test_input_stage_full_batch_properties():
     # three samples against the oracle
     ref = oin.input_stage_oracle(images[5:8].numpy(), boxes[5:8].numpy(), np.zeros(3, bool), 224, 224, mean, std)
     assert np.array_equal(a[5:8].float().cpu().permute(0, 2, 3, 1).numpy(), _bf16_round(ref))
+
+
+# ------------------------------------------------------------------------------------------------ K6
+@pytest.mark.parametrize("shape", [(2, 8, 8, 8), (3, 16, 7, 9), (2, 64, 12, 5), (1, 8, 1, 1), (2, 24, 2, 3)])
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_maxpool_matches_oracle(shape, dtype):
+    n, c, h, w = shape
+    g = torch.Generator().manual_seed(h * 100 + w)
+    x = torch.randn(n, h, w, c, generator=g).relu().to(dtype)       # post-ReLU: many exact ties at 0
+    x[0, 0, 0, :] = float("-inf") if h * w > 1 else x[0, 0, 0, :]
+    xd = x.to(DEV).permute(0, 3, 1, 2)
+    y, arg = cabi.maxpool_fwd(xd)
+    yo, pos = omp.maxpool3x3s2_fwd_oracle(x.float().numpy())
+    assert np.array_equal(y.float().cpu().permute(0, 2, 3, 1).numpy(), yo)   # max of inputs: exact
+    assert np.array_equal(arg.cpu().numpy(), pos)                            # argmax incl. tie rule: exact
+    dy = torch.randn(yo.shape, generator=g).to(dtype)
+    dx = cabi.maxpool_bwd(dy.to(DEV).permute(0, 3, 1, 2), arg, xd.shape)
+    dxo = omp.maxpool3x3s2_bwd_oracle(dy.float().numpy(), pos, (h, w))
+    got = dx.float().cpu().permute(0, 2, 3, 1).numpy()
+    if dtype == torch.float32:
+        assert np.allclose(got, dxo, rtol=1e-6, atol=1e-6)
+    else:
+        assert np.abs(got - dxo).max() <= np.abs(dxo).max() * 2 ** -8 + 1e-9
+
+
+def test_maxpool_full_size_against_aten():
+    """BASELINE size [256,64,112,112] bf16: the library kernel the reference would have run is the
+    checker here (max values and routed gradients must agree exactly / to one bf16 rounding)."""
+    g = torch.Generator(device=DEV).manual_seed(0)
+    x = torch.randn(256, 112, 112, 64, device=DEV, generator=g).relu().to(torch.bfloat16).permute(0, 3, 1, 2)
+    y, arg = cabi.maxpool_fwd(x)
+    yr, idx = torch.ops.aten.max_pool2d_with_indices(x, [3, 3], [2, 2], [1, 1], [1, 1], False)
+    assert torch.equal(y, yr)
+    dy = torch.randn(256, 56, 56, 64, device=DEV, generator=g).to(torch.bfloat16).permute(0, 3, 1, 2)
+    dx = cabi.maxpool_bwd(dy, arg, x.shape)
+    dxr = torch.ops.aten.max_pool2d_with_indices_backward(dy, x, [3, 3], [2, 2], [1, 1], [1, 1], False, idx)
+    assert (dx.float() - dxr.float()).abs().max().item() <= dxr.float().abs().max().item() * 2 ** -7
+
+
+def test_input_stage_space_to_depth_layout_is_a_reindexing():
+    rng = np.random.default_rng(3)
+    n, sh, sw, oh, ow = 4, 90, 70, 64, 48
+    images = rng.integers(0, 256, (n, sh, sw, 3), dtype=np.uint8)
+    from imagent_distributed_training_pytorch_with_slurm_b200.data import draw_batch_params
+    boxes, flips = draw_batch_params(n, sh, sw, torch.Generator().manual_seed(1))
+    mean, std = (0.485, 0.456, 0.406), (0.229, 0.224, 0.225)
+    ref = oin.input_stage_oracle(images, boxes.numpy(), flips.numpy().astype(bool), oh, ow, mean, std)
+    want = oin.space_to_depth_stem_oracle(ref)
+    for dtype in (torch.float32, torch.bfloat16):
+        out = cabi.input_stage(torch.from_numpy(images).to(DEV), boxes.to(DEV), flips.to(DEV), oh, ow, mean, std, dtype,
+                               cabi.LAYOUT_S2D_STEM)
+        assert out.shape == (n, 16, (oh + 6) // 2, (ow + 6) // 2) and out._b200_s2d_stem == (oh, ow)
+        got = out.float().cpu().permute(0, 2, 3, 1).numpy()
+        assert np.array_equal(got, want if dtype == torch.float32 else _bf16_round(want))

@@ -147,3 +147,30 @@ def test_train_and_validate_loops_with_device_input_stage():
     b = b200.train(l2, m2, crit, o2, 0, 1, sync_every=1)
     assert a[0] == pytest.approx(b[0], rel=2e-2) and a[1] == b[1]  # (bit-equality is checked on CPU; cuDNN
     # wgrad is not run-to-run deterministic)
+
+
+def test_space_to_depth_stem_equals_plain_stem():
+    """Same batch through the 7x7/2 stem and through the rearranged 4x4/1 stem (float32): logits,
+    loss and the conv1 weight gradient agree to convolution rounding."""
+    from imagent_distributed_training_pytorch_with_slurm_b200 import _cabi
+    g = torch.Generator().manual_seed(0)
+    n, src, out = 8, 80, 64
+    images = torch.randint(0, 256, (n, src, src, 3), dtype=torch.uint8, generator=g).cuda()
+    boxes, flips = b200.draw_batch_params(n, src, src, g)
+    target = torch.randint(0, 1000, (n,), generator=g).cuda()
+    mean, std = b200.data.IMAGENET_MEAN, b200.data.IMAGENET_STD
+    res = []
+    for layout in (_cabi.LAYOUT_NHWC, _cabi.LAYOUT_S2D_STEM):
+        torch.manual_seed(0)
+        model = b200.build_model("resnet18", dtype=torch.float32).cuda().train()
+        x = _cabi.input_stage(images, boxes.cuda(), flips.cuda(), out, out, mean, std, torch.float32, layout)
+        logits = model(x)
+        loss = b200.CrossEntropyLoss()(logits, target)
+        loss.backward()
+        res.append((logits.detach().clone(), loss.item(), model.conv1.weight.grad.detach().clone(),
+                    model.fc.weight.grad.detach().clone()))
+    a, b = res
+    assert torch.allclose(a[0], b[0], rtol=1e-3, atol=1e-3)
+    assert abs(a[1] - b[1]) <= 1e-4 * abs(a[1])
+    for i in (2, 3):
+        assert ((a[i] - b[i]).norm() / a[i].norm()).item() < 5e-3
