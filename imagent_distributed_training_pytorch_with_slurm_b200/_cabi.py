@@ -29,6 +29,7 @@ SIGNATURES = {
     "b200_sgd_flat_f32": (_i32, [_vp, _vp, _vp, _vp, _i64, _f32, _f32, _f32, _f32, _i32, _vp]),
     "b200_ce_topk_workspace_bytes": (_sz, [_i64]),
     "b200_ce_topk_fwd": (_i32, [_vp, _vp, _vp, _vp, _vp, _sz, _i64, _i64, _i32, _vp]),
+    "b200_ce_topk_fwd_static": (_i32, [_vp, _vp, _vp, _vp, _i64, _i64, _i32, _vp]),
     "b200_ce_bwd": (_i32, [_vp, _vp, _vp, _vp, _f32, _vp, _i64, _i64, _i32, _vp]),
     "b200_bn_vec": (_i32, [_i32]),
     "b200_bn_workspace_bytes": (_sz, [_i64, _i32, _i32]),
@@ -194,6 +195,31 @@ def ce_topk_fwd(logits, target, out3=None):
                                 dtype_code(logits), _stream()), "b200_ce_topk_fwd")
     stats.end("ce_topk_fwd", 1, s, n * c * logits.element_size() + 8 * n + 12)
     return out3, row_lse
+
+
+CE_STATIC_MAX_ROWS = 16384
+
+
+def ce_topk_fwd_static(logits, target, out3, row_lse):
+    """Loss + top-1/top-5 like ``ce_topk_fwd`` for code paths that must not allocate: nothing is
+    allocated here either (no torch tensor is created; ``out3`` float32[3] and ``row_lse`` float32[N] are
+    the caller's), and the kernel's scratch is a fixed array inside the library.  Meant for hooks that
+    run when the process may no longer ask the driver or PyTorch's allocator for device memory.  At most
+    ``CE_STATIC_MAX_ROWS`` rows; calls that could overlap on the GPU must not share a device.  The first
+    call on a device should happen outside stream capture."""
+    _need_cuda(logits, target, out3, row_lse)
+    n, c = logits.shape
+    if n > CE_STATIC_MAX_ROWS:
+        raise B200Error(f"b200_ce_topk_fwd_static handles at most {CE_STATIC_MAX_ROWS} rows (its built-in scratch is "
+                        f"fixed-size); got {n}. Use ce_topk_fwd, which takes a workspace.")
+    if not (logits.is_contiguous() and target.is_contiguous() and target.dtype == torch.int64 and target.numel() == n):
+        raise B200Error("logits [N,C] contiguous and int64 target [N] expected")
+    if not (out3.dtype == torch.float32 and out3.numel() == 3 and out3.is_contiguous()
+            and row_lse.dtype == torch.float32 and row_lse.numel() == n and row_lse.is_contiguous()):
+        raise B200Error("out3 must be float32[3] and row_lse float32[N], both preallocated by the caller")
+    _check(load().b200_ce_topk_fwd_static(_ptr(logits), _ptr(target), _ptr(out3), _ptr(row_lse), n, c,
+                                          dtype_code(logits), _stream()), "b200_ce_topk_fwd_static")
+    stats.launches += 1
 
 
 def ce_bwd(logits, target, row_lse, grad_out=None, scale=1.0):

@@ -7,6 +7,8 @@
 // nll_loss, topk, transpose, eq, 2x(reshape,float,sum,mul)) and a bit-reproducible sum.
 #include <math.h>
 
+#include <mutex>
+
 #include "common.cuh"
 
 namespace {
@@ -223,6 +225,61 @@ extern "C" int b200_ce_bwd(const void *logits, const int64_t *target, const floa
         ce_bwd_kernel<__nv_bfloat16><<<blocks, kWarpsPerBlock * 32, 0, st>>>(
             static_cast<const __nv_bfloat16 *>(logits), target, row_lse, grad_out, scale,
             static_cast<__nv_bfloat16 *>(dlogits), n, c, vec_ok);
+    B200_CHECK_LAUNCH();
+    return 0;
+}
+
+// ------------------------------------------------------------------------------------------------
+// Loss + top-1/top-5 for hosts that cannot hand in a workspace (see the header for who that is).
+// The scratch the kernel needs (a 16-byte ticket and three floats per row) lives in this array, which
+// every GPU that loads the library carries until the process exits: 16 + 12 * 16384 = 196,624 bytes.
+static __device__ __align__(256) unsigned char g_ce_static_scratch[16 + sizeof(float) * 3 * B200_CE_STATIC_MAX_ROWS];
+
+namespace {
+constexpr int kMaxDevices = 64;
+// In host code `g_ce_static_scratch` is only a handle for the runtime, not an address a kernel can
+// use; the real device address differs per GPU and is looked up once per device, below.
+void *g_ce_static_addr[kMaxDevices] = {};
+std::mutex g_ce_static_mutex;
+}  // namespace
+
+extern "C" int b200_ce_topk_fwd_static(const void *logits, const int64_t *target, float *out3, float *row_lse,
+                                       int64_t n, int64_t c, int dtype, void *stream) {
+    if (!logits || !target || !out3 || !row_lse || n <= 0 || c <= 0) return (int)cudaErrorInvalidValue;
+    if (dtype != B200_F32 && dtype != B200_BF16) return (int)cudaErrorInvalidValue;
+    if (n > B200_CE_STATIC_MAX_ROWS) return (int)cudaErrorInvalidValue;  // more rows than the built-in scratch holds
+    if (b200_misaligned(logits)) return (int)cudaErrorMisalignedAddress;
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return (int)e;
+    if (dev < 0 || dev >= kMaxDevices) return (int)cudaErrorInvalidDevice;
+    void *scratch = nullptr;
+    {
+        std::lock_guard<std::mutex> lock(g_ce_static_mutex);
+        scratch = g_ce_static_addr[dev];
+        if (!scratch) {  // first call on this GPU (it is the current device): resolve the array's address here
+            e = cudaGetSymbolAddress(&scratch, g_ce_static_scratch);
+            if (e != cudaSuccess) return (int)e;
+            g_ce_static_addr[dev] = scratch;
+        }
+    }
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    // The array still holds whatever the previous call left.  Only the ticket has to start at zero (the
+    // per-row slots of rows < n are all overwritten before they are read), so clear just that.
+    e = cudaMemsetAsync(scratch, 0, 16, st);
+    if (e != cudaSuccess) return (int)e;
+    unsigned *ticket = static_cast<unsigned *>(scratch);
+    float *rows = reinterpret_cast<float *>(static_cast<char *>(scratch) + 16);
+    const int blocks = (int)((n + kWarpsPerBlock - 1) / kWarpsPerBlock);
+    const float pct = (float)(100.0 / (double)n);
+    const size_t esz = dtype == B200_F32 ? 4 : 2;
+    const bool vec_ok = ((size_t)c * esz) % 16 == 0;
+    if (dtype == B200_F32)
+        ce_topk_fwd_kernel<float><<<blocks, kWarpsPerBlock * 32, 0, st>>>(
+            static_cast<const float *>(logits), target, out3, row_lse, ticket, rows, n, c, pct, vec_ok);
+    else
+        ce_topk_fwd_kernel<__nv_bfloat16><<<blocks, kWarpsPerBlock * 32, 0, st>>>(
+            static_cast<const __nv_bfloat16 *>(logits), target, out3, row_lse, ticket, rows, n, c, pct, vec_ok);
     B200_CHECK_LAUNCH();
     return 0;
 }

@@ -82,6 +82,28 @@ size_t b200_ce_topk_workspace_bytes(int64_t n);
 int b200_ce_topk_fwd(const void *logits, const int64_t *target, float *out3, float *row_lse, void *workspace,
                      size_t workspace_bytes, int64_t n, int64_t c, int dtype, void *stream);
 
+/* The same loss + top-1/top-5 computation for callers that cannot supply a workspace.
+ * (This entry point has no counterpart in the reference.)
+ * Who needs it: host code that is not allowed to obtain device memory when it wants a loss value and has
+ * no scratch buffer of its own to pass - for example a metrics or validation hook that runs after the
+ * training framework has claimed all of HBM for its own pool, or a monitoring thread that must not call
+ * cudaMalloc/cudaFree because those stall every stream of the device while they run.  The scratch comes
+ * out of the library image instead: a fixed array of 16 + 12*B200_CE_STATIC_MAX_ROWS = 196,624 bytes that
+ * every GPU loading the library holds until the process ends.  The call itself allocates and frees
+ * nothing (no cudaMalloc/cudaFree, no allocating library routine); logits, target, out3 and row_lse are
+ * still the caller's buffers, with the same meaning as in b200_ce_topk_fwd.
+ *   - n must not exceed B200_CE_STATIC_MAX_ROWS; a larger batch is refused with cudaErrorInvalidValue
+ *     before anything is launched (use b200_ce_topk_fwd with your own workspace for those).
+ *   - The first call on each GPU looks up that GPU's address of the array (the GPU must be the current
+ *     device, as for every call here); make that first call before starting any stream capture.
+ *   - All calls on a GPU share the one array.  Each call re-zeroes the 16-byte ticket on `stream` and
+ *     rewrites the per-row slots it uses, so back-to-back calls on one stream are fine; two calls that
+ *     can overlap on the GPU (different streams, no dependency) race on the array and give garbage.
+ */
+#define B200_CE_STATIC_MAX_ROWS 16384
+int b200_ce_topk_fwd_static(const void *logits, const int64_t *target, float *out3, float *row_lse, int64_t n,
+                            int64_t c, int dtype, void *stream);
+
 /* Backward of the loss above (loss.backward(), imagenet.py:128, first node):
  *     dlogits[n][j] = (exp(x_nj - row_lse[n]) - [j == t_n]) * scale * (grad_out ? *grad_out : 1) / N
  * grad_out is a DEVICE scalar (the upstream gradient, 1.0 for loss.backward()) or NULL; scale is a
