@@ -146,6 +146,8 @@ def run_ours(a):
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=dev)
     torch.backends.cudnn.benchmark = True
+    if os.environ.get("B200_CUDNN_BENCH_LIMIT"):
+        torch.backends.cudnn.benchmark_limit = int(os.environ["B200_CUDNN_BENCH_LIMIT"])
     dtype = torch.float32 if a.fp32 else torch.bfloat16
 
     torch.manual_seed(0)

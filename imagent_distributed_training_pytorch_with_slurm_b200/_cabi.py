@@ -36,9 +36,10 @@ SIGNATURES = {
     "b200_bn_fwd_train": (_i32, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _sz, _i64, _i32, _f32, _f32,
                                  _i32, _i32, _vp]),
     "b200_bn_fwd_eval": (_i32, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _i64, _i32, _f32, _i32, _i32, _vp]),
-    "b200_bn_bwd": (_i32, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _sz, _i64, _i32, _i32, _i32, _vp]),
+    "b200_bn_bwd": (_i32, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _sz, _i64, _i32, _i32, _i32, _vp]),
     "b200_maxpool3x3s2_fwd": (_i32, [_vp, _vp, _vp, _i64, _i32, _i32, _i32, _i32, _vp]),
     "b200_maxpool3x3s2_bwd": (_i32, [_vp, _vp, _vp, _i64, _i32, _i32, _i32, _i32, _vp]),
+    "b200_pack_grads": (_i32, [_c.POINTER(_vp), _c.POINTER(_i64), _c.POINTER(_i64), _i32, _vp, _f32, _i32, _vp]),
     "b200_input_workspace_bytes": (_sz, [_i64, _i32, _i32, _i32, _i32]),
     "b200_input_crop_resize_flip_norm": (_i32, [_vp, _vp, _vp, _vp, _vp, _sz, _i64, _i32, _i32, _i32, _i32,
                                                 _c.POINTER(_f32), _c.POINTER(_f32), _i32, _i32, _vp]),
@@ -288,10 +289,16 @@ def bn_fwd_eval(x, z, gamma, beta, running_mean, running_var, eps, act):
     return y
 
 
-def bn_bwd(dy, x, mask, gamma, saved, act, dgamma=None, dbeta=None):
+_NOT_SUPPORTED = 801  # cudaErrorNotSupported
+
+
+def bn_bwd(dy, x, mask, gamma, saved, act, dgamma=None, dbeta=None, dy2=None):
     """Returns (dx, dz or None, dgamma, dbeta); dgamma/dbeta may be preallocated float32 views
-    (e.g. slices of the flat gradient buffer) and are overwritten."""
-    _need_cuda(dy, x, gamma, saved)
+    (e.g. slices of the flat gradient buffer) and are overwritten.  ``dy2``: optional second gradient
+    branch, summed with ``dy`` inside the kernels (residual fan-in)."""
+    _need_cuda(dy, x, gamma, saved, dy2)
+    if dy2 is not None and (dy2.shape != dy.shape or dy2.dtype != dy.dtype or dy2.stride() != dy.stride()):
+        raise B200Error("dy2 must match dy")
     m, c = _rows_channels(x)
     if dy.shape != x.shape or dy.dtype != x.dtype:
         raise B200Error("dy must match x")
@@ -307,11 +314,36 @@ def bn_bwd(dy, x, mask, gamma, saved, act, dgamma=None, dbeta=None):
     nbytes = lib.b200_bn_workspace_bytes(m, c, dt)
     ws = workspace(x.device, nbytes, "bn")
     s = stats.begin("bn_bwd")
-    _check(lib.b200_bn_bwd(_ptr(dy), _ptr(x), _ptr(mask), _ptr(gamma), _ptr(saved), _ptr(dx), _ptr(dz), _ptr(dgamma),
-                           _ptr(dbeta), _ptr(ws), ws.numel(), m, c, act, dt, _stream()), "b200_bn_bwd")
+    args = (_ptr(x), _ptr(mask), _ptr(gamma), _ptr(saved), _ptr(dx), _ptr(dz), _ptr(dgamma), _ptr(dbeta), _ptr(ws),
+            ws.numel(), m, c, act, dt, _stream())
+    rc = lib.b200_bn_bwd(_ptr(dy), _ptr(dy2), *args)
+    if rc == _NOT_SUPPORTED and dy2 is not None:  # shape outside the bulk-async kernels: add the branches first
+        dy = dy + dy2
+        rc = lib.b200_bn_bwd(_ptr(dy), None, *args)
+    _check(rc, "b200_bn_bwd")
     e = m * c * x.element_size()
-    stats.end("bn_bwd", 3, s, (6 if act == ACT_ADD_RELU else 5) * e + (2 * (mask.numel() - 16) if mask is not None else 0))
+    # algorithmic bytes: the two-pass model of SURVEY 8d; a second gradient branch is read in both passes
+    # (+2E: it replaces the separate add kernel's 3E)
+    stats.end("bn_bwd", 3, s, ((6 if act == ACT_ADD_RELU else 5) + (2 if dy2 is not None else 0)) * e
+              + (2 * (mask.numel() - 16) if mask is not None else 0))
     return dx, dz, dgamma, dbeta
+
+
+# ---- K5 -------------------------------------------------------------------------------------------
+def pack_grads(tensors, offsets, dst, scale=1.0):
+    """Cast-copy each tensor (all of one dtype, each dense in memory) to ``dst[offset : offset+numel]``
+    (float32 flat buffer) in one launch per 64 tensors."""
+    if not tensors:
+        return
+    _need_cuda(dst, *tensors)
+    n = len(tensors)
+    dt = dtype_code(tensors[0])
+    srcs = (_vp * n)(*[t.data_ptr() for t in tensors])
+    offs = (_i64 * n)(*[int(o) for o in offsets])
+    cnts = (_i64 * n)(*[t.numel() for t in tensors])
+    s = stats.begin("pack")
+    _check(load().b200_pack_grads(srcs, offs, cnts, n, _ptr(dst), scale, dt, _stream()), "b200_pack_grads")
+    stats.end("pack", (n + 63) // 64, s, sum(t.numel() * (t.element_size() + 4) for t in tensors))
 
 
 # ---- K6 -------------------------------------------------------------------------------------------

@@ -579,10 +579,11 @@ int fwd_eval_impl(const void *x_, const void *z_, void *y_, const float *gamma, 
 }
 
 template <typename T, int VEC>
-int bwd_impl(const void *dy_, const void *x_, const uint8_t *mask, const float *gamma, const float *saved, void *dx_,
+int bwd_impl(const void *dy_, const void *dy2_, const void *x_, const uint8_t *mask, const float *gamma, const float *saved, void *dx_,
              void *dz_, float *dgamma, float *dbeta, void *ws, size_t ws_bytes, int64_t m, int c, int act,
              cudaStream_t st) {
     const T *dy = static_cast<const T *>(dy_);
+    const T *dy2 = static_cast<const T *>(dy2_);
     const T *x = static_cast<const T *>(x_);
     T *dx = static_cast<T *>(dx_);
     T *dz = static_cast<T *>(dz_);
@@ -590,25 +591,31 @@ int bwd_impl(const void *dy_, const void *x_, const uint8_t *mask, const float *
         if (act == B200_ACT_ADD_RELU && b200_misaligned(mask)) return (int)cudaErrorMisalignedAddress;
         const size_t red_bytes = sizeof(float) * kThreads * 2 * VEC;
         const bool masked = act == B200_ACT_ADD_RELU;
-        const PipeGeom pr = make_geom_pipe(m, c, VEC, sizeof(T), 2, masked, red_bytes);
-        const PipeGeom pa = make_geom_pipe(m, c, VEC, sizeof(T), 2, masked, 0);
+        const int nt = dy2 ? 3 : 2;
+        const PipeGeom pr = make_geom_pipe(m, c, VEC, sizeof(T), nt, masked, red_bytes);
+        const PipeGeom pa = make_geom_pipe(m, c, VEC, sizeof(T), nt, masked, 0);
         const Geom &g = pr.g;
         if (ws_bytes < ws_bytes_for(g, c)) return (int)cudaErrorInvalidValue;
         const Ws w = carve(ws, g, c);
 #define B200_BWD_PIPE(ACT)                                                                                        \
     do {                                                                                                          \
-        auto kr = bn_bwd_reduce_pipe_kernel<T, VEC, ACT>;                                                         \
-        auto ka = bn_bwd_apply_pipe_kernel<T, VEC, ACT>;                                                          \
+        if (dy2) B200_BWD_PIPE2(ACT, true);                                                                       \
+        else B200_BWD_PIPE2(ACT, false);                                                                          \
+    } while (0)
+#define B200_BWD_PIPE2(ACT, DY2)                                                                                  \
+    do {                                                                                                          \
+        auto kr = bn_bwd_reduce_pipe_kernel<T, VEC, ACT, DY2>;                                                    \
+        auto ka = bn_bwd_apply_pipe_kernel<T, VEC, ACT, DY2>;                                                     \
         cudaError_t e = allow_smem(kr, pr.smem);                                                                  \
         if (e == cudaSuccess) e = allow_smem(ka, pa.smem);                                                        \
         if (e != cudaSuccess) return (int)e;                                                                      \
-        kr<<<g.nchunk, kThreads, pr.smem, st>>>(dy, x, mask, saved, w.partial, m, c, g.txl, g.nchunk, g.rpc,      \
+        kr<<<g.nchunk, kThreads, pr.smem, st>>>(dy, dy2, x, mask, saved, w.partial, m, c, g.txl, g.nchunk, g.rpc, \
                                                 g_bn_stats_reverse, pr.stages);                                   \
         B200_CHECK_LAUNCH();                                                                                      \
         bn_bwd_finalize_kernel<<<(c + kWarps - 1) / kWarps, kThreads, 0, st>>>(w.partial, g.nchunk, m, c, gamma,   \
                                                                               saved, dgamma, dbeta, w.coef);     \
         B200_CHECK_LAUNCH();                                                                                      \
-        ka<<<pa.g.nchunk, kThreads, pa.smem, st>>>(dy, x, mask, saved, w.coef, dx, dz, m, c, pa.g.txl,            \
+        ka<<<pa.g.nchunk, kThreads, pa.smem, st>>>(dy, dy2, x, mask, saved, w.coef, dx, dz, m, c, pa.g.txl,       \
                                                    pa.g.nchunk, pa.g.rpc, g_bn_apply_reverse, pa.stages);         \
         B200_CHECK_LAUNCH();                                                                                      \
     } while (0)
@@ -616,8 +623,10 @@ int bwd_impl(const void *dy_, const void *x_, const uint8_t *mask, const float *
         else if (act == B200_ACT_RELU) B200_BWD_PIPE(B200_ACT_RELU);
         else B200_BWD_PIPE(B200_ACT_ADD_RELU);
 #undef B200_BWD_PIPE
+#undef B200_BWD_PIPE2
         return 0;
     }
+    if (dy2) return (int)cudaErrorNotSupported;  // two-branch gradients only in the bulk-async kernels
     const Geom g = make_geom(m, c, VEC, Unroll<T, VEC>::U);
     if (ws_bytes < ws_bytes_for(g, c)) return (int)cudaErrorInvalidValue;
     const Ws w = carve(ws, g, c);
@@ -733,7 +742,7 @@ extern "C" int b200_bn_fwd_eval(const void *x, const void *z, void *y, const flo
     return fwd_eval_impl<__nv_bfloat16, 4>(x, z, y, gamma, beta, running_mean, running_var, m, c, eps, act, st);
 }
 
-extern "C" int b200_bn_bwd(const void *dy, const void *x, const uint8_t *mask, const float *gamma, const float *saved,
+extern "C" int b200_bn_bwd(const void *dy, const void *dy2, const void *x, const uint8_t *mask, const float *gamma, const float *saved,
                            void *dx, void *dz, float *dgamma, float *dbeta, void *workspace, size_t workspace_bytes,
                            int64_t m, int c, int act, int dtype, void *stream) {
     const int vec = b200_bn_vec(dtype);
@@ -741,15 +750,15 @@ extern "C" int b200_bn_bwd(const void *dy, const void *x, const uint8_t *mask, c
     if (e) return e;
     if (!dy || !x || !gamma || !saved || !dx || !workspace) return (int)cudaErrorInvalidValue;
     if (act == B200_ACT_ADD_RELU && (!mask || !dz)) return (int)cudaErrorInvalidValue;
-    if (b200_misaligned(dy) || b200_misaligned(x) || b200_misaligned(dx) || b200_misaligned(dz) ||
+    if (b200_misaligned(dy) || b200_misaligned(dy2) || b200_misaligned(x) || b200_misaligned(dx) || b200_misaligned(dz) ||
         b200_misaligned(workspace))
         return (int)cudaErrorMisalignedAddress;
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     if (dtype == B200_F32)
-        return bwd_impl<float, 4>(dy, x, mask, gamma, saved, dx, dz, dgamma, dbeta, workspace, workspace_bytes, m, c, act, st);
+        return bwd_impl<float, 4>(dy, dy2, x, mask, gamma, saved, dx, dz, dgamma, dbeta, workspace, workspace_bytes, m, c, act, st);
     if (vec == 8)
-        return bwd_impl<__nv_bfloat16, 8>(dy, x, mask, gamma, saved, dx, dz, dgamma, dbeta, workspace, workspace_bytes, m,
+        return bwd_impl<__nv_bfloat16, 8>(dy, dy2, x, mask, gamma, saved, dx, dz, dgamma, dbeta, workspace, workspace_bytes, m,
                                           c, act, st);
-    return bwd_impl<__nv_bfloat16, 4>(dy, x, mask, gamma, saved, dx, dz, dgamma, dbeta, workspace, workspace_bytes, m, c,
+    return bwd_impl<__nv_bfloat16, 4>(dy, dy2, x, mask, gamma, saved, dx, dz, dgamma, dbeta, workspace, workspace_bytes, m, c,
                                       act, st);
 }

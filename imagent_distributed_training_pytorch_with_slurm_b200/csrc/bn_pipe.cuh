@@ -256,9 +256,10 @@ bn_apply_pipe_kernel(const T *__restrict__ x, const T *__restrict__ z, T *__rest
 }
 
 // ---- backward pass 1 ---------------------------------------------------------------------------
-template <typename T, int VEC, int ACT>
+template <typename T, int VEC, int ACT, bool DY2>
 __global__ void __launch_bounds__(kThreads)
-bn_bwd_reduce_pipe_kernel(const T *__restrict__ dy, const T *__restrict__ x, const uint8_t *__restrict__ mask,
+bn_bwd_reduce_pipe_kernel(const T *__restrict__ dy, const T *__restrict__ dy2, const T *__restrict__ x,
+                          const uint8_t *__restrict__ mask,
                           const float *__restrict__ saved, float2 *__restrict__ partial, int64_t m, int c, int txl,
                           int nchunk, int64_t rpc, int reverse, int nstages) {
     extern __shared__ __align__(128) unsigned char dyn_smem[];
@@ -271,9 +272,11 @@ bn_bwd_reduce_pipe_kernel(const T *__restrict__ dy, const T *__restrict__ x, con
     const int chunk = reverse ? (nchunk - 1 - (int)blockIdx.x) : (int)blockIdx.x;
     const int64_t r0 = (int64_t)chunk * rpc;
     const int64_t r1 = (r0 + rpc < m) ? (r0 + rpc) : m;
-    TileRing<2, MASK> ring;
+    constexpr int NT = DY2 ? 3 : 2;
+    TileRing<NT, MASK> ring;
     ring.src[0] = reinterpret_cast<const unsigned char *>(dy);
     ring.src[1] = reinterpret_cast<const unsigned char *>(x);
+    if (DY2) ring.src[NT - 1] = reinterpret_cast<const unsigned char *>(dy2);
     ring.msrc = mask;
     ring.setup(dyn_smem, txl, nstages, (int64_t)c * sizeof(T), r0, r1);
     float mean[VEC], sc[VEC], sf[VEC];
@@ -290,6 +293,7 @@ bn_bwd_reduce_pipe_kernel(const T *__restrict__ dy, const T *__restrict__ x, con
         const int nrows = ring.wait(t, s, (uint32_t)ph);
         const uint4 *tg = reinterpret_cast<const uint4 *>(ring.stage(s, 0));
         const uint4 *tv = reinterpret_cast<const uint4 *>(ring.stage(s, 1));
+        const uint4 *tg2 = reinterpret_cast<const uint4 *>(ring.stage(s, NT - 1));
         const unsigned char *tm = ring.mstage(s);
 #pragma unroll
         for (int u = 0; u < kPipeU; ++u) {
@@ -298,6 +302,12 @@ bn_bwd_reduce_pipe_kernel(const T *__restrict__ dy, const T *__restrict__ x, con
                 float g[VEC], e[VEC];
                 unpack16<T, VEC>(tg[v], g);
                 unpack16<T, VEC>(tv[v], e);
+                if (DY2) {  // the incoming gradient is the sum of two branches (residual fan-in)
+                    float g2[VEC];
+                    unpack16<T, VEC>(tg2[v], g2);
+#pragma unroll
+                    for (int k = 0; k < VEC; ++k) g[k] += g2[k];
+                }
                 const unsigned bits = MASK ? tm[v] : 0u;
 #pragma unroll
                 for (int k = 0; k < VEC; ++k) {
@@ -320,9 +330,10 @@ bn_bwd_reduce_pipe_kernel(const T *__restrict__ dy, const T *__restrict__ x, con
 }
 
 // ---- backward pass 3 ---------------------------------------------------------------------------
-template <typename T, int VEC, int ACT>
+template <typename T, int VEC, int ACT, bool DY2>
 __global__ void __launch_bounds__(kThreads)
-bn_bwd_apply_pipe_kernel(const T *__restrict__ dy, const T *__restrict__ x, const uint8_t *__restrict__ mask,
+bn_bwd_apply_pipe_kernel(const T *__restrict__ dy, const T *__restrict__ dy2, const T *__restrict__ x,
+                         const uint8_t *__restrict__ mask,
                          const float *__restrict__ saved, const float *__restrict__ coef, T *__restrict__ dx,
                          T *__restrict__ dz, int64_t m, int c, int txl, int nchunk, int64_t rpc, int reverse, int nstages) {
     extern __shared__ __align__(128) unsigned char dyn_smem[];
@@ -334,9 +345,11 @@ bn_bwd_apply_pipe_kernel(const T *__restrict__ dy, const T *__restrict__ x, cons
     const int chunk = reverse ? (nchunk - 1 - (int)blockIdx.x) : (int)blockIdx.x;
     const int64_t r0 = (int64_t)chunk * rpc;
     const int64_t r1 = (r0 + rpc < m) ? (r0 + rpc) : m;
-    TileRing<2, MASK> ring;
+    constexpr int NT = DY2 ? 3 : 2;
+    TileRing<NT, MASK> ring;
     ring.src[0] = reinterpret_cast<const unsigned char *>(dy);
     ring.src[1] = reinterpret_cast<const unsigned char *>(x);
+    if (DY2) ring.src[NT - 1] = reinterpret_cast<const unsigned char *>(dy2);
     ring.msrc = mask;
     ring.setup(dyn_smem, txl, nstages, (int64_t)c * sizeof(T), r0, r1);
     float mean[VEC], c0[VEC], c1[VEC], c2[VEC], sc[VEC], sf[VEC];
@@ -354,6 +367,7 @@ bn_bwd_apply_pipe_kernel(const T *__restrict__ dy, const T *__restrict__ x, cons
         const int nrows = ring.wait(t, s, (uint32_t)ph);
         const uint4 *tg = reinterpret_cast<const uint4 *>(ring.stage(s, 0));
         const uint4 *tv = reinterpret_cast<const uint4 *>(ring.stage(s, 1));
+        const uint4 *tg2 = reinterpret_cast<const uint4 *>(ring.stage(s, NT - 1));
         const unsigned char *tm = ring.mstage(s);
         const int64_t row0 = r0 + (int64_t)t * ring.rows_per_tile;
 #pragma unroll
@@ -364,6 +378,12 @@ bn_bwd_apply_pipe_kernel(const T *__restrict__ dy, const T *__restrict__ x, cons
                 float g[VEC], e[VEC];
                 unpack16<T, VEC>(tg[v], g);
                 unpack16<T, VEC>(tv[v], e);
+                if (DY2) {
+                    float g2[VEC];
+                    unpack16<T, VEC>(tg2[v], g2);
+#pragma unroll
+                    for (int k = 0; k < VEC; ++k) g[k] += g2[k];
+                }
                 const unsigned bits = MASK ? tm[v] : 0u;
 #pragma unroll
                 for (int k = 0; k < VEC; ++k) {

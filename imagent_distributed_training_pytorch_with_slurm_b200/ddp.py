@@ -54,6 +54,10 @@ class FlatDDP(nn.Module):
             a.refresh_shadow()
 
     # ---- called by the model's backward ---------------------------------------------------------
+    def wants(self, offset):
+        """True when gradients at arena offsets >= ``offset`` being final completes a bucket."""
+        return (self.world_size > 1 and self._next < len(self.buckets) and self.buckets[self._next][0] >= offset)
+
     def grad_ready(self, offset):
         if self.world_size == 1:
             return

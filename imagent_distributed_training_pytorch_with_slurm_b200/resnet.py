@@ -67,6 +67,8 @@ class _Conv(nn.Module):
         self.weight = None  # set by _adopt
         self.w_compute = None
         self.grad_view = None
+        self.grad_offset = 0   # element offset of this weight's slot in the gradient arena
+        self.pending = None    # list shared with the network: (wgrad tensor, arena offset) awaiting one pack launch
 
     def fwd(self, x):
         return torch.ops.aten.convolution(x, self.w_compute, None, self.stride, self.padding, self.dilation, False,
@@ -76,7 +78,11 @@ class _Conv(nn.Module):
         gx, gw, _ = torch.ops.aten.convolution_backward(gy, x, self.w_compute, None, self.stride, self.padding,
                                                         self.dilation, False, (0, 0), self.groups,
                                                         (need_gx, True, False))
-        self.grad_view.copy_(gw)
+        dense = gw.is_contiguous(memory_format=torch.channels_last) if gw.dim() == 4 else gw.is_contiguous()
+        if self.pending is not None and dense:
+            self.pending.append((gw, self.grad_offset))  # K,R,S,C memory order == the arena slot's order
+        else:
+            self.grad_view.copy_(gw)
         return gx
 
 
@@ -131,8 +137,8 @@ class _BN(nn.Module):
     def fwd_eval(self, x, act, z=None):
         return _cabi.bn_fwd_eval(x, z, self.weight, self.bias, self.running_mean, self.running_var, self.eps, act)
 
-    def bwd(self, dy, x, saved, mask, act):
-        dx, dz, _, _ = _cabi.bn_bwd(dy, x, mask, self.weight, saved, act, self.g_weight, self.g_bias)
+    def bwd(self, dy, x, saved, mask, act, dy2=None):
+        dx, dz, _, _ = _cabi.bn_bwd(dy, x, mask, self.weight, saved, act, self.g_weight, self.g_bias, dy2)
         return dx, dz
 
 
@@ -196,10 +202,14 @@ class _Block(nn.Module):
         return bn.fwd_eval(t, _cabi.ACT_ADD_RELU, zd)
 
     def bwd(self, g_out, tape, need_gx=True):
+        """``g_out``: gradient of the block output, either one tensor or the pair (main branch,
+        identity branch) left un-added by the block after this one - the BatchNorm backward kernels sum
+        the pair on the fly.  Returns such a pair for the block before."""
         pairs = self.convs()
         conv, bn = pairs[-1]
-        g, g_z = bn.bwd(g_out, tape["x"].pop(), tape["saved"].pop(), tape.pop("mask"), _cabi.ACT_ADD_RELU)
-        del g_out
+        g_out, g_out2 = g_out if isinstance(g_out, tuple) else (g_out, None)
+        g, g_z = bn.bwd(g_out, tape["x"].pop(), tape["saved"].pop(), tape.pop("mask"), _cabi.ACT_ADD_RELU, g_out2)
+        del g_out, g_out2
         for conv_prev, bn_prev in reversed(pairs[:-1]):
             g = conv.bwd(g, tape["a"].pop())
             g, _ = bn_prev.bwd(g, tape["x"].pop(), tape["saved"].pop(), None, _cabi.ACT_RELU)
@@ -212,9 +222,7 @@ class _Block(nn.Module):
             g2 = self.downsample[0].bwd(g_td, x_in, need_gx)
         else:
             g2 = g_z
-        if need_gx:
-            g.add_(g2)
-        return g
+        return (g, g2) if need_gx else None
 
 
 class _WholeNet(torch.autograd.Function):
@@ -272,6 +280,7 @@ class B200ResNet(nn.Module):
     # ---- storage --------------------------------------------------------------------------------
     def _adopt(self, tv):
         """Move the torchvision module's parameters/buffers into flat arenas, keeping key order."""
+        self.__dict__["_pending"] = []
         tv_params = dict(tv.named_parameters())
         tv_mods = dict(tv.named_modules())
         names = [n for n, _ in tv.named_parameters()]
@@ -311,6 +320,7 @@ class B200ResNet(nn.Module):
                 setattr(m, leaf, p)
                 if isinstance(m, _Conv):
                     m.grad_view = a.view(a.grads, i)
+                    m.grad_offset, m.pending = a.offsets[i], self._pending
                     m.w_compute = a.view(a.shadow, i) if a.shadow is not None else p.detach()
                 elif isinstance(m, _BN):
                     if leaf == "weight":
@@ -332,6 +342,21 @@ class B200ResNet(nn.Module):
     def mark_offsets(self):
         """Arena offsets (descending) at which gradients become final during the backward."""
         return sorted(set(self._marks.values()) | {0}, reverse=True)
+
+    def _flush_grads(self):
+        """One K5 launch writes every weight gradient produced since the last flush into the arena."""
+        if self._pending:
+            _cabi.pack_grads([t for t, _ in self._pending], [o for _, o in self._pending], self.arena.grads)
+            self._pending.clear()
+
+    def _progress(self, offset):
+        """Backward has finished everything at arena offsets >= ``offset``."""
+        sink = self._sink
+        if sink is not None and sink.wants(offset):
+            self._flush_grads()
+            sink.grad_ready(offset)
+        elif offset == 0:
+            self._flush_grads()
 
     def attach_sink(self, sink):
         self.__dict__["_sink"] = sink  # bypass nn.Module registration (the wrapper owns us, not vice versa)
@@ -408,8 +433,7 @@ class B200ResNet(nn.Module):
         else:
             fc.g_weight.copy_(torch.addmm(fc.w_compute, g_logits.t(), feat, beta=0.0, alpha=pre))
             fc.g_bias.copy_(g_logits.sum(0, dtype=torch.float32) * pre)
-        if sink is not None:
-            sink.grad_ready(self._marks["fc"])
+        self._progress(self._marks["fc"])
         n, c, h, w = tape.pop("last_shape")
         g = (g_feat * (1.0 / (h * w))).view(n, c, 1, 1).expand(n, c, h, w).contiguous(memory_format=torch.channels_last)
         blocks = tape.pop("blocks")
@@ -417,8 +441,8 @@ class B200ResNet(nn.Module):
             layer = getattr(self, f"layer{li}")
             for bi in range(len(layer) - 1, -1, -1):
                 g = layer[bi].bwd(g, blocks.pop())
-                if sink is not None:
-                    sink.grad_ready(self._marks[(li, bi)])
+                self._progress(self._marks[(li, bi)])
+        g = g[0].add_(g[1])  # the stem has no BatchNorm behind the first block to absorb the sum
         g = _cabi.maxpool_bwd(g, tape.pop("pool_idx"), tape.pop("pool_in_shape"))
         g, _ = self.bn1.bwd(g, tape.pop("t1"), tape.pop("saved1"), None, _cabi.ACT_RELU)
         stem = tape.pop("stem")
@@ -426,8 +450,9 @@ class B200ResNet(nn.Module):
             stem.bwd(g, tape.pop("x0"), need_gx=False)
         else:
             stem.bwd(g, tape.pop("x0"))
+        self._progress(0)
+        self._flush_grads()
         if sink is not None:
-            sink.grad_ready(0)
             sink.backward_done()
 
 

@@ -150,8 +150,13 @@ int b200_bn_fwd_eval(const void *x, const void *z, void *y, const float *gamma, 
  * three launches (per-chunk sums -> finalize -> apply).  The ReLU mask is recomputed from x and
  * saved{scale,shift} for B200_ACT_RELU, read from `mask` for B200_ACT_ADD_RELU.  dgamma/dbeta are
  * written (not accumulated) as float32 - they may point straight into a flat gradient buffer.
+ * dy2 (nullable): a second gradient tensor of the same shape; the incoming gradient is then dy + dy2
+ * (summed in float32 on the fly).  This is the residual fan-in of `out += identity`
+ * (resnet.py:102,160): the block output's gradient arrives from the next block's first convolution
+ * AND from its identity branch, and autograd would add the two with a separate kernel.  Only the
+ * bulk-async kernels take dy2; other shapes return cudaErrorNotSupported (add the tensors first).
  */
-int b200_bn_bwd(const void *dy, const void *x, const uint8_t *mask, const float *gamma, const float *saved,
+int b200_bn_bwd(const void *dy, const void *dy2, const void *x, const uint8_t *mask, const float *gamma, const float *saved,
                 void *dx, void *dz, float *dgamma, float *dbeta, void *workspace, size_t workspace_bytes,
                 int64_t m, int c, int act, int dtype, void *stream);
 
@@ -199,6 +204,18 @@ int b200_maxpool3x3s2_fwd(const void *x, void *y, uint8_t *argmax, int64_t n, in
                           void *stream);
 int b200_maxpool3x3s2_bwd(const void *dy, const uint8_t *argmax, void *dx, int64_t n, int c, int h, int w, int dtype,
                           void *stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * K5  gradient packing: many weight-gradient tensors -> their slots of one flat float32 buffer.
+ * Replaces the per-parameter `bucket_view.copy_(grad)` / `mul_out(grad, 1/W)` of DDP's Reducer
+ * (reducer.hpp:347-406,497-500; driven by loss.backward(), imagenet.py:128) with one launch per flush:
+ * tensor i has counts[i] contiguous elements of `src_dtype` at srcs[i] (DEVICE pointer, 16-byte aligned)
+ * and lands at dst + offsets[i] (offsets in elements, multiples of 4), multiplied by `scale`.
+ * srcs / offsets / counts are HOST arrays of length n_tensors; they are copied into kernel parameters
+ * (64 tensors per launch), so nothing is allocated and the arrays may be reused as soon as the call returns.
+ */
+int b200_pack_grads(const void *const *srcs, const int64_t *offsets, const int64_t *counts, int n_tensors, float *dst,
+                    float scale, int src_dtype, void *stream);
 
 #ifdef __cplusplus
 }

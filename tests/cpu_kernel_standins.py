@@ -50,7 +50,9 @@ def bn_fwd_eval(x, z, gamma, beta, running_mean, running_var, eps, act):
     return _like(y, x)
 
 
-def bn_bwd(dy, x, mask, gamma, saved, act, dgamma=None, dbeta=None):
+def bn_bwd(dy, x, mask, gamma, saved, act, dgamma=None, dbeta=None, dy2=None):
+    if dy2 is not None:
+        dy = dy + dy2
     xr = _rows(x).float().numpy()
     mean, invstd, scale, shift = (saved[i].numpy() for i in range(4))
     if act == obn.ACT_RELU:
@@ -114,3 +116,10 @@ def maxpool_fwd(x):
 def maxpool_bwd(dy, arg, in_shape):
     dx = omp.maxpool3x3s2_bwd_oracle(dy.permute(0, 2, 3, 1).float().numpy(), arg.numpy(), (in_shape[2], in_shape[3]))
     return torch.from_numpy(dx).to(dy.dtype).permute(0, 3, 1, 2)
+
+
+def pack_grads(tensors, offsets, dst, scale=1.0):
+    for t, o in zip(tensors, offsets):
+        n = t.numel()
+        flat = t.permute(0, 2, 3, 1).reshape(-1) if t.dim() == 4 else t.reshape(-1)  # memory (K,R,S,C) order
+        dst[o:o + n].copy_(flat.float() * scale)

@@ -169,6 +169,16 @@ def _bn_check(m, c, act, dtype, vec, seed, eps=1e-5, momentum=0.1):
         assert np.allclose(dxk[safe], dxo[safe], rtol=1e-4, atol=1e-5 * (np.abs(dxo).max() + 1))
     if act == cabi.ACT_ADD_RELU:
         assert np.array_equal(dz.float().cpu().numpy()[safe], (dys * pos)[safe])  # masked copy: exact
+    # two-branch incoming gradient (residual fan-in): same result as adding the branches first
+    half = (dyd.float() * 0.5).to(dtype)
+    rest = (dyd.float() - half.float()).to(dtype)
+    if torch.equal((half.float() + rest.float()).to(dtype), dyd):
+        dx2, dz2, dg2, db2 = cabi.bn_bwd(half, xd, mask, gd, saved, act, dy2=rest)
+        if bf:
+            assert (dx2.float() - dx.float()).abs().max().item() <= np.abs(dxo).max() * 2 ** -7
+        else:
+            assert torch.allclose(dx2, dx, rtol=1e-5, atol=1e-6)
+        assert torch.allclose(dg2, dg, rtol=1e-4, atol=1e-4 * scale + 1e-3)
     # eval mode with the updated running statistics
     ye = cabi.bn_fwd_eval(xd, zd if act == cabi.ACT_ADD_RELU else None, gd, bd, rm, rv, eps, act)
     yeo = obn.bn_eval_fwd_oracle(xs, gamma, beta, rm.cpu().numpy(), rv.cpu().numpy(), eps, act, zs)
@@ -382,3 +392,25 @@ def test_input_stage_space_to_depth_layout_is_a_reindexing():
         assert out.shape == (n, 16, (oh + 6) // 2, (ow + 6) // 2) and out._b200_s2d_stem == (oh, ow)
         got = out.float().cpu().permute(0, 2, 3, 1).numpy()
         assert np.array_equal(got, want if dtype == torch.float32 else _bf16_round(want))
+
+
+# ------------------------------------------------------------------------------------------------ K5
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float32])
+def test_pack_grads_matches_per_tensor_copies(dtype):
+    g = torch.Generator().manual_seed(0)
+    shapes = [(64, 3, 7, 7), (64, 64, 1, 1), (128, 64, 3, 3), (1000, 512), (7,), (13, 5, 3, 3)] + [(8, 8, 1, 1)] * 70
+    tensors, offsets, off = [], [], 0
+    for shp in shapes:
+        t = torch.randn(*shp, generator=g).to(dtype).to(DEV)
+        if len(shp) == 4:
+            t = t.contiguous(memory_format=torch.channels_last)
+        tensors.append(t)
+        offsets.append(off)
+        off += (t.numel() + 31) // 32 * 32
+    dst = torch.full((off,), 7.0, device=DEV)
+    cabi.pack_grads(tensors, offsets, dst, 0.5)
+    want = torch.full((off,), 7.0, device=DEV)
+    for t, o in zip(tensors, offsets):
+        flat = t.permute(0, 2, 3, 1).reshape(-1) if t.dim() == 4 else t.reshape(-1)
+        want[o:o + t.numel()] = flat.float() * 0.5
+    assert torch.equal(dst, want)   # cast + power-of-two scale: exact; padding between slots untouched
