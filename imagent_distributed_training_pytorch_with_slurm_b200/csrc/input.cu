@@ -97,23 +97,39 @@ __device__ __forceinline__ __nv_bfloat16 cast_out<__nv_bfloat16>(float v) { retu
 
 struct Norm { float mean[3]; float std[3]; };
 
+// One CTA = one tile of 8 output rows of one sample.  Output rows of a tile are assembled in shared
+// memory in their final memory layout and leave with 16-byte vector stores (NHWC: 8 contiguous rows;
+// space-to-depth: 4 complete rows of 16-channel cells, border and spare channels included - the tile
+// origin is shifted by the 3-pixel padding so that cells are never split between CTAs).
 template <typename OutT>
 __global__ void __launch_bounds__(kThreads)
 input_resample_kernel(const uint8_t *__restrict__ images, const int32_t *__restrict__ boxes,
                       const uint8_t *__restrict__ flips, OutT *__restrict__ out, const int32_t *__restrict__ ws,
                       int src_h, int src_w, int out_h, int out_w, int KX, int KY, int max_src_rows, Norm nrm,
-                      int layout) {
+                      int layout, int inter_bytes) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     float *lut = reinterpret_cast<float *>(smem_raw);          // [3][256]
     uint8_t *inter = smem_raw + 3 * 256 * sizeof(float);       // [max_src_rows][out_w][3]
+    OutT *otile = reinterpret_cast<OutT *>(inter + inter_bytes);  // staged output tile (NHWC / S2D only)
 
     const int64_t s = blockIdx.y;
-    const int y0 = blockIdx.x * kTileRows;
-    const int y1 = (y0 + kTileRows < out_h) ? y0 + kTileRows : out_h;
+    const bool s2d = layout == B200_LAYOUT_S2D_STEM;
+    const int ya = (int)blockIdx.x * kTileRows - (s2d ? 3 : 0);   // first output row of the tile (may be < 0)
+    const int y0 = ya < 0 ? 0 : ya;
+    const int y1 = (ya + kTileRows < out_h) ? ya + kTileRows : out_h;
+    const int sy = (out_h + 6) >> 1, sx = (out_w + 6) >> 1;
     for (int i = threadIdx.x; i < 3 * 256; i += kThreads) {
         const int ch = i >> 8, v = i & 255;
         // ToTensor: float32(v) / 255 ; Normalize: (x - mean) / std, all IEEE float32
         lut[i] = __fdiv_rn(__fsub_rn(__fdiv_rn((float)v, 255.0f), nrm.mean[ch]), nrm.std[ch]);
+    }
+    // staged tile geometry
+    const int cell_rows = s2d ? ((sy - (int)blockIdx.x * 4 < 4) ? sy - (int)blockIdx.x * 4 : 4) : 0;
+    const int tile_elems = s2d ? cell_rows * sx * 16 : (layout == B200_LAYOUT_NHWC ? (y1 - y0) * out_w * 3 : 0);
+    if (s2d) {  // border cells and the 4 spare channels read as zero
+        uint32_t *z = reinterpret_cast<uint32_t *>(otile);
+        const int words = tile_elems * (int)sizeof(OutT) / 4;
+        for (int i = threadIdx.x; i < words; i += kThreads) z[i] = 0u;
     }
     const int64_t per_sample = (int64_t)out_w * (2 + KX) + (int64_t)out_h * (2 + KY);
     const int32_t *bx = ws + s * per_sample;
@@ -122,69 +138,106 @@ input_resample_kernel(const uint8_t *__restrict__ images, const int32_t *__restr
     const int32_t *cy = by + 2 * out_h;
     const int top = boxes[s * 4 + 0], left = boxes[s * 4 + 1];
     const bool flip = flips && flips[s] != 0;
-    const int ylo = by[2 * y0];
-    const int nrows = by[2 * (y1 - 1)] + by[2 * (y1 - 1) + 1] - ylo;
-    if (nrows > max_src_rows) return;  // contract violation (box outside the stated limits)
+    if (y1 > y0) {
+        const int ylo = by[2 * y0];
+        const int nrows = by[2 * (y1 - 1)] + by[2 * (y1 - 1) + 1] - ylo;
+        if (nrows > max_src_rows) return;  // contract violation (box outside the stated limits)
 
-    // horizontal pass: needed source rows -> 8-bit intermediate in shared memory
-    const uint8_t *img = images + ((int64_t)s * src_h + top + ylo) * (int64_t)src_w * 3 + (int64_t)left * 3;
-    for (int idx = threadIdx.x; idx < nrows * out_w; idx += kThreads) {
-        const int rr = idx / out_w, xx = idx - rr * out_w;
-        const int xmin = bx[2 * xx], cnt = bx[2 * xx + 1];
-        const uint8_t *px = img + (int64_t)rr * src_w * 3 + xmin * 3;
-        const int32_t *k = cx + (int64_t)xx * KX;
-        int a0 = 1 << (kPrecisionBits - 1), a1 = a0, a2 = a0;
-        for (int t = 0; t < cnt; ++t) {
-            const int kk = k[t];
-            a0 += (int)px[3 * t + 0] * kk;
-            a1 += (int)px[3 * t + 1] * kk;
-            a2 += (int)px[3 * t + 2] * kk;
+        // horizontal pass: a thread owns an output column, keeps that column's taps in registers and
+        // walks down the needed source rows -> 8-bit intermediate in shared memory
+        const uint8_t *img = images + ((int64_t)s * src_h + top + ylo) * (int64_t)src_w * 3 + (int64_t)left * 3;
+        for (int xx = threadIdx.x; xx < out_w; xx += kThreads) {
+            const int xmin = bx[2 * xx], cnt = bx[2 * xx + 1];
+            const int32_t *k = cx + (int64_t)xx * KX;
+            int kk[8];
+#pragma unroll
+            for (int t = 0; t < 8; ++t) kk[t] = (t < cnt) ? k[t] : 0;
+            const uint8_t *px = img + xmin * 3;
+            if (cnt <= 8) {
+                for (int rr = 0; rr < nrows; ++rr, px += (int64_t)src_w * 3) {
+                    int a0 = 1 << (kPrecisionBits - 1), a1 = a0, a2 = a0;
+#pragma unroll
+                    for (int t = 0; t < 8; ++t) {
+                        if (t < cnt) {
+                            a0 += (int)px[3 * t + 0] * kk[t];
+                            a1 += (int)px[3 * t + 1] * kk[t];
+                            a2 += (int)px[3 * t + 2] * kk[t];
+                        }
+                    }
+                    uint8_t *o = inter + (rr * out_w + xx) * 3;
+                    o[0] = (uint8_t)clip8(a0);
+                    o[1] = (uint8_t)clip8(a1);
+                    o[2] = (uint8_t)clip8(a2);
+                }
+            } else {  // very strong down-scaling: taps stay in memory
+                for (int rr = 0; rr < nrows; ++rr, px += (int64_t)src_w * 3) {
+                    int a0 = 1 << (kPrecisionBits - 1), a1 = a0, a2 = a0;
+                    for (int t = 0; t < cnt; ++t) {
+                        const int kt = k[t];
+                        a0 += (int)px[3 * t + 0] * kt;
+                        a1 += (int)px[3 * t + 1] * kt;
+                        a2 += (int)px[3 * t + 2] * kt;
+                    }
+                    uint8_t *o = inter + (rr * out_w + xx) * 3;
+                    o[0] = (uint8_t)clip8(a0);
+                    o[1] = (uint8_t)clip8(a1);
+                    o[2] = (uint8_t)clip8(a2);
+                }
+            }
         }
-        uint8_t *o = inter + (rr * out_w + xx) * 3;
-        o[0] = (uint8_t)clip8(a0);
-        o[1] = (uint8_t)clip8(a1);
-        o[2] = (uint8_t)clip8(a2);
+        __syncthreads();
+
+        // vertical pass -> flip -> normalise -> staged tile (or straight to memory for NCHW)
+        const int npix = (y1 - y0) * out_w;
+        for (int idx = threadIdx.x; idx < npix; idx += kThreads) {
+            const int ry = idx / out_w, xx = idx - ry * out_w;
+            const int yy = y0 + ry;
+            const int ymin = by[2 * yy] - ylo, cnt = by[2 * yy + 1];
+            const int32_t *k = cy + (int64_t)yy * KY;
+            int a0 = 1 << (kPrecisionBits - 1), a1 = a0, a2 = a0;
+            for (int t = 0; t < cnt; ++t) {
+                const int kt = k[t];
+                const uint8_t *p = inter + ((ymin + t) * out_w + xx) * 3;
+                a0 += (int)p[0] * kt;
+                a1 += (int)p[1] * kt;
+                a2 += (int)p[2] * kt;
+            }
+            const float f0 = lut[clip8(a0)], f1 = lut[256 + clip8(a1)], f2 = lut[512 + clip8(a2)];
+            const int xd = flip ? (out_w - 1 - xx) : xx;
+            if (layout == B200_LAYOUT_NHWC) {
+                OutT *o = otile + (ry * out_w + xd) * 3;
+                o[0] = cast_out<OutT>(f0);
+                o[1] = cast_out<OutT>(f1);
+                o[2] = cast_out<OutT>(f2);
+            } else if (s2d) {
+                // image zero-padded by 3, then 2x2 space-to-depth: pixel (py,px) -> cell (py/2,px/2),
+                // channels (py%2*2 + px%2)*3 + ch of a 16-channel cell (12 used, 4 stay zero)
+                const int py = yy + 3, px = xd + 3;
+                OutT *o = otile + ((((py >> 1) - (int)blockIdx.x * 4) * sx + (px >> 1)) << 4) + ((py & 1) * 2 + (px & 1)) * 3;
+                o[0] = cast_out<OutT>(f0);
+                o[1] = cast_out<OutT>(f1);
+                o[2] = cast_out<OutT>(f2);
+            } else {
+                const int64_t plane = (int64_t)out_h * out_w;
+                OutT *o = out + (int64_t)s * 3 * plane + (int64_t)yy * out_w + xd;
+                o[0] = cast_out<OutT>(f0);
+                o[plane] = cast_out<OutT>(f1);
+                o[2 * plane] = cast_out<OutT>(f2);
+            }
+        }
     }
+    if (tile_elems == 0) return;
     __syncthreads();
-
-    // vertical pass -> flip -> normalise -> store
-    const int npix = (y1 - y0) * out_w;
-    for (int idx = threadIdx.x; idx < npix; idx += kThreads) {
-        const int ry = idx / out_w, xx = idx - ry * out_w;
-        const int yy = y0 + ry;
-        const int ymin = by[2 * yy] - ylo, cnt = by[2 * yy + 1];
-        const int32_t *k = cy + (int64_t)yy * KY;
-        int a0 = 1 << (kPrecisionBits - 1), a1 = a0, a2 = a0;
-        for (int t = 0; t < cnt; ++t) {
-            const int kk = k[t];
-            const uint8_t *p = inter + ((ymin + t) * out_w + xx) * 3;
-            a0 += (int)p[0] * kk;
-            a1 += (int)p[1] * kk;
-            a2 += (int)p[2] * kk;
-        }
-        const float f0 = lut[clip8(a0)], f1 = lut[256 + clip8(a1)], f2 = lut[512 + clip8(a2)];
-        const int xd = flip ? (out_w - 1 - xx) : xx;
-        if (layout == B200_LAYOUT_NHWC) {
-            OutT *o = out + (((int64_t)s * out_h + yy) * out_w + xd) * 3;
-            o[0] = cast_out<OutT>(f0);
-            o[1] = cast_out<OutT>(f1);
-            o[2] = cast_out<OutT>(f2);
-        } else if (layout == B200_LAYOUT_S2D_STEM) {
-            // image zero-padded by 3, then 2x2 space-to-depth: pixel (py,px) -> cell (py/2,px/2),
-            // channels (py%2*2 + px%2)*3 + ch of a 16-channel cell (12 used, 4 stay zero)
-            const int py = yy + 3, px = xd + 3;
-            const int sy = (out_h + 6) >> 1, sx = (out_w + 6) >> 1;
-            OutT *o = out + ((((int64_t)s * sy + (py >> 1)) * sx + (px >> 1)) << 4) + ((py & 1) * 2 + (px & 1)) * 3;
-            o[0] = cast_out<OutT>(f0);
-            o[1] = cast_out<OutT>(f1);
-            o[2] = cast_out<OutT>(f2);
-        } else {
-            const int64_t plane = (int64_t)out_h * out_w;
-            OutT *o = out + (int64_t)s * 3 * plane + (int64_t)yy * out_w + xd;
-            o[0] = cast_out<OutT>(f0);
-            o[plane] = cast_out<OutT>(f1);
-            o[2 * plane] = cast_out<OutT>(f2);
-        }
+    // copy the staged tile out: it is one contiguous span of the output tensor
+    OutT *dst = s2d ? out + (((int64_t)s * sy + (int64_t)blockIdx.x * 4) * sx << 4)
+                    : out + ((int64_t)s * out_h + y0) * out_w * 3;
+    const int bytes = tile_elems * (int)sizeof(OutT);
+    if (((reinterpret_cast<uintptr_t>(dst) | (uintptr_t)bytes) & 15) == 0) {
+        const uint4 *sv = reinterpret_cast<const uint4 *>(otile);
+        uint4 *dv = reinterpret_cast<uint4 *>(dst);
+        for (int i = threadIdx.x; i < bytes / 16; i += kThreads) dv[i] = sv[i];
+    } else {
+        for (int i = threadIdx.x; i < tile_elems; i += kThreads) dst[i] = otile[i];
     }
 }
 
@@ -223,17 +276,19 @@ extern "C" int b200_input_crop_resize_flip_norm(const uint8_t *images, const int
     input_coeff_kernel<<<(unsigned)((items + kThreads - 1) / kThreads), kThreads, 0, st>>>(boxes, n, out_h, out_w, KX,
                                                                                            KY, ws);
     B200_CHECK_LAUNCH();
-    if (out_layout == B200_LAYOUT_S2D_STEM) {  // border cells and the 4 spare channels must read as zero
-        const size_t bytes = (size_t)n * ((out_h + 6) / 2) * ((out_w + 6) / 2) * 16 * (out_dtype == B200_F32 ? 4 : 2);
-        cudaError_t e = cudaMemsetAsync(out, 0, bytes, st);
-        if (e != cudaSuccess) return (int)e;
-    }
     const int max_rows = max_src_rows_for(src_h, out_h);
-    const size_t smem = 3 * 256 * sizeof(float) + (size_t)max_rows * out_w * 3;
+    const size_t esz = out_dtype == B200_F32 ? 4 : 2;
+    const int inter_bytes = (int)(((size_t)max_rows * out_w * 3 + 15) / 16 * 16);
+    size_t tile_bytes = 0;
+    if (out_layout == B200_LAYOUT_NHWC) tile_bytes = (size_t)kTileRows * out_w * 3 * esz;
+    if (out_layout == B200_LAYOUT_S2D_STEM) tile_bytes = (size_t)4 * ((out_w + 6) / 2) * 16 * esz;
+    const size_t smem = 3 * 256 * sizeof(float) + (size_t)inter_bytes + tile_bytes;
     if (smem > 200 * 1024) return (int)cudaErrorInvalidValue;
     Norm nrm;
     for (int i = 0; i < 3; ++i) { nrm.mean[i] = mean3[i]; nrm.std[i] = std3[i]; }
-    const dim3 grid((out_h + kTileRows - 1) / kTileRows, (unsigned)n);
+    const int tiles = out_layout == B200_LAYOUT_S2D_STEM ? (out_h + 6 + kTileRows - 1) / kTileRows
+                                                         : (out_h + kTileRows - 1) / kTileRows;
+    const dim3 grid(tiles, (unsigned)n);
     if (out_dtype == B200_F32) {
         auto kern = input_resample_kernel<float>;
         if (smem > 48 * 1024) {
@@ -241,7 +296,7 @@ extern "C" int b200_input_crop_resize_flip_norm(const uint8_t *images, const int
             if (e != cudaSuccess) return (int)e;
         }
         kern<<<grid, kThreads, smem, st>>>(images, boxes, flips, static_cast<float *>(out), ws, src_h, src_w, out_h,
-                                           out_w, KX, KY, max_rows, nrm, out_layout);
+                                           out_w, KX, KY, max_rows, nrm, out_layout, inter_bytes);
     } else {
         auto kern = input_resample_kernel<__nv_bfloat16>;
         if (smem > 48 * 1024) {
@@ -249,7 +304,7 @@ extern "C" int b200_input_crop_resize_flip_norm(const uint8_t *images, const int
             if (e != cudaSuccess) return (int)e;
         }
         kern<<<grid, kThreads, smem, st>>>(images, boxes, flips, static_cast<__nv_bfloat16 *>(out), ws, src_h, src_w,
-                                           out_h, out_w, KX, KY, max_rows, nrm, out_layout);
+                                           out_h, out_w, KX, KY, max_rows, nrm, out_layout, inter_bytes);
     }
     B200_CHECK_LAUNCH();
     return 0;

@@ -81,47 +81,69 @@ maxpool_fwd_kernel(const T *__restrict__ x, T *__restrict__ y, uint8_t *__restri
     *reinterpret_cast<uint2 *>(arg + gid * 8) = packed;
 }
 
+// Backward as a gather over 2x2 input patches: the patch {2p, 2p+1} x {2q, 2q+1} is touched by exactly
+// the four windows (p..p+1) x (q..q+1), so a thread loads those four (gradient, argmax) vectors once and
+// produces four output vectors.
 template <typename T>
 __global__ void __launch_bounds__(kThreads)
 maxpool_bwd_kernel(const T *__restrict__ dy, const uint8_t *__restrict__ arg, T *__restrict__ dx, int64_t total, int c8,
                    int h, int w, int oh, int ow) {
     const int64_t gid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (gid >= total) return;
+    const int ph = (h + 1) >> 1, pw = (w + 1) >> 1;
     const int cv = (int)(gid % c8);
     int64_t r = gid / c8;
-    const int ix = (int)(r % w); r /= w;
-    const int iy = (int)(r % h);
-    const int64_t n = r / h;
-    float acc[8];
+    const int px = (int)(r % pw); r /= pw;
+    const int py = (int)(r % ph);
+    const int64_t n = r / ph;
+    const int c = c8 * 8;
+    float g[2][2][8];
+    unsigned pos[2][2][8];
 #pragma unroll
-    for (int k = 0; k < 8; ++k) acc[k] = 0.f;
-    // windows containing row iy: oy with 2*oy-1 <= iy <= 2*oy+1  ->  oy in {iy/2, (iy+1)/2}
-    const int oy0 = iy >> 1, oy1 = (iy + 1) >> 1;
-    const int ox0 = ix >> 1, ox1 = (ix + 1) >> 1;
-#pragma unroll
-    for (int a = 0; a < 2; ++a) {
-        const int oy = a ? oy1 : oy0;
-        if (a && oy1 == oy0) continue;
-        if (oy >= oh) continue;
-        const int kh = iy - (oy * 2 - 1);
+    for (int a = 0; a < 2; ++a)
 #pragma unroll
         for (int b = 0; b < 2; ++b) {
-            const int ox = b ? ox1 : ox0;
-            if (b && ox1 == ox0) continue;
-            if (ox >= ow) continue;
-            const unsigned me = (unsigned)(kh * 3 + (ix - (ox * 2 - 1)));
-            const int64_t o = (((n * oh + oy) * ow + ox) * c8 + cv) * 8;
-            const uint2 p = *reinterpret_cast<const uint2 *>(arg + o);
-            float g[8];
-            V8<T>::load(dy + o, g);
+            const int oy = py + a, ox = px + b;
+            if (oy < oh && ox < ow) {
+                const int64_t o = (((n * oh + oy) * ow + ox) * c8 + cv) * 8;
+                const uint2 p = *reinterpret_cast<const uint2 *>(arg + o);
+                V8<T>::load(dy + o, g[a][b]);
 #pragma unroll
-            for (int k = 0; k < 8; ++k) {
-                const unsigned pk = ((k < 4 ? p.x : p.y) >> ((k & 3) * 8)) & 0xffu;
-                if (pk == me) acc[k] += g[k];
+                for (int k = 0; k < 8; ++k) pos[a][b][k] = ((k < 4 ? p.x : p.y) >> ((k & 3) * 8)) & 0xffu;
+            } else {
+#pragma unroll
+                for (int k = 0; k < 8; ++k) { g[a][b][k] = 0.f; pos[a][b][k] = 0xffu; }
             }
         }
+    // pixel (2py+i, 2px+j): window (py+a, px+b) contains it at (kh, kw) = (i+1-2a, j+1-2b) when both are in 0..2
+#pragma unroll
+    for (int i = 0; i < 2; ++i) {
+        const int iy = 2 * py + i;
+        if (iy >= h) continue;
+#pragma unroll
+        for (int j = 0; j < 2; ++j) {
+            const int ix = 2 * px + j;
+            if (ix >= w) continue;
+            float acc[8];
+#pragma unroll
+            for (int k = 0; k < 8; ++k) acc[k] = 0.f;
+#pragma unroll
+            for (int a = 0; a < 2; ++a) {
+                const int kh = i + 1 - 2 * a;
+                if (kh < 0 || kh > 2) continue;
+#pragma unroll
+                for (int b = 0; b < 2; ++b) {
+                    const int kw = j + 1 - 2 * b;
+                    if (kw < 0 || kw > 2) continue;
+                    const unsigned me = (unsigned)(kh * 3 + kw);
+#pragma unroll
+                    for (int k = 0; k < 8; ++k)
+                        if (pos[a][b][k] == me) acc[k] += g[a][b][k];
+                }
+            }
+            V8<T>::store(dx + ((n * h + iy) * w + ix) * c + cv * 8, acc);
+        }
     }
-    V8<T>::store(dx + gid * 8, acc);
 }
 
 }  // namespace
@@ -152,7 +174,7 @@ extern "C" int b200_maxpool3x3s2_bwd(const void *dy, const uint8_t *argmax, void
     if (dtype != B200_F32 && dtype != B200_BF16) return (int)cudaErrorInvalidValue;
     if (b200_misaligned(dy) || b200_misaligned(dx) || b200_misaligned(argmax, 8)) return (int)cudaErrorMisalignedAddress;
     const int oh = (h + 2 - 3) / 2 + 1, ow = (w + 2 - 3) / 2 + 1;
-    const int64_t total = n * h * w * (c / 8);
+    const int64_t total = n * ((h + 1) / 2) * ((w + 1) / 2) * (c / 8);
     const unsigned blocks = (unsigned)((total + kThreads - 1) / kThreads);
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     if (dtype == B200_BF16)

@@ -137,10 +137,10 @@ class SyntheticImageNet:
             self._fixed = out
         return out
 
-    def _upload(self, slot, first_use):
+    def _upload(self, slot, first_use, params):
         """Enqueue the H2D copies of one step on the side stream."""
         dev = self.stage.device
-        boxes, flips, target = self._params()
+        boxes, flips, target = params
         with torch.cuda.stream(self._stream):
             if not first_use:
                 self._stream.wait_event(slot["free"])  # the kernel that read this slot has finished
@@ -149,6 +149,28 @@ class SyntheticImageNet:
             slot["flips"] = flips.to(dev, non_blocking=True)
             slot["target"] = target.to(dev, non_blocking=True)
             slot["ready"].record(self._stream)
+
+    def _param_stream(self):
+        """Per-step (boxes, flips, target) drawn by a helper thread a few steps ahead of the consumer, in
+        the same order a single thread would draw them (the generator is only touched by the helper)."""
+        import queue
+        import threading
+
+        q = queue.Queue(maxsize=4)
+
+        def work():
+            try:
+                for _ in range(self.steps):
+                    q.put(self._params())
+            except BaseException as e:  # surface errors in the consumer
+                q.put(e)
+
+        threading.Thread(target=work, daemon=True).start()
+        for _ in range(self.steps):
+            item = q.get()
+            if isinstance(item, BaseException):
+                raise item
+            yield item
 
     def __iter__(self):
         dev = self.stage.device
@@ -159,12 +181,13 @@ class SyntheticImageNet:
                 yield x, target.to(dev, non_blocking=True)
             return
         main = torch.cuda.current_stream(dev)
+        params = self._param_stream()
         if self.steps > 0:
-            self._upload(self._slots[0], True)
+            self._upload(self._slots[0], True, next(params))
         for i in range(self.steps):
             slot = self._slots[i % 2]
             if i + 1 < self.steps:
-                self._upload(self._slots[(i + 1) % 2], i + 1 < 2)
+                self._upload(self._slots[(i + 1) % 2], i + 1 < 2, next(params))
             main.wait_event(slot["ready"])
             x = _cabi.input_stage(slot["img"], slot["boxes"], slot["flips"], self.stage.out_h, self.stage.out_w,
                                   self.stage.mean, self.stage.std, self.stage.dtype, self.stage.layout)

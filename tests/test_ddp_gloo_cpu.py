@@ -73,5 +73,7 @@ def test_flatddp_two_ranks_match_stock_ddp_golden():
         assert r0["l2"][k] == pytest.approx(v, rel=5e-3 if k.endswith("bn2.bias") else 2e-4), k
         assert r0["l2"][k] == pytest.approx(r1["l2"][k], rel=1e-6), k
     assert r0["nbt"] == gold["nbt"] == gold["steps"]
+    # BatchNorm buffers: rank 0's running statistics were broadcast to rank 1 (DDP _sync_buffers)
+    assert r0["bn_rv"] == r1["bn_rv"]
     # buckets: several slices covering the arena, first (last layers) starts communication early
     assert r0["n_buckets"] >= 3 and sum(r0["bucket_bytes"]) >= 46_758_048
