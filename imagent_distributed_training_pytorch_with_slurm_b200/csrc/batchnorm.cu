@@ -35,6 +35,7 @@ int g_bn_apply_reverse = 0;
 int g_bn_pipeline = 1;       // 1 = bulk-async (TMA) shared-memory ring kernels where eligible, 0 = direct loads
 int g_bn_pipe_ctas_per_sm = 2;
 int g_bn_pipe_stages = 0;    // 0 = automatic
+int g_bn_pdl = 1;            // finalize / apply kernels of the bulk-async path use programmatic dependent launch
 
 template <typename T, int VEC>
 struct Unroll {
@@ -162,6 +163,23 @@ cudaError_t allow_smem(K kern, size_t bytes) {
     return cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
 }
 
+// Launch `kern`; with `dependent` (and the knob on) it carries the programmatic-stream-serialization
+// attribute, i.e. it may begin while the previous kernel of the stream is still draining (see pdl_wait).
+template <typename... KArgs, typename... Args>
+cudaError_t launch(void (*kern)(KArgs...), unsigned grid, size_t smem, cudaStream_t st, bool dependent, Args... args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(grid);
+    cfg.blockDim = dim3(kThreads);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = (dependent && g_bn_pdl) ? 1 : 0;
+    return cudaLaunchKernelEx(&cfg, kern, static_cast<KArgs>(args)...);
+}
+
 // ------------------------------------------------------------------------------------------------
 // forward pass 1: per-(channel, chunk) mean and M2
 template <typename T, int VEC>
@@ -223,6 +241,8 @@ bn_fwd_finalize_kernel(const float2 *__restrict__ partial, int nchunk, int64_t r
                        const float *__restrict__ gamma, const float *__restrict__ beta, float *__restrict__ rmean,
                        float *__restrict__ rvar, int64_t *__restrict__ nbt, float *__restrict__ saved, float eps,
                        float momentum) {
+    pdl_trigger();
+    pdl_wait();
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int ch = blockIdx.x * kWarps + warp;
     if (blockIdx.x == 0 && threadIdx.x == 0 && nbt) *nbt += 1;
@@ -381,6 +401,8 @@ __global__ void __launch_bounds__(kThreads)
 bn_bwd_finalize_kernel(const float2 *__restrict__ partial, int nchunk, int64_t m, int c,
                        const float *__restrict__ gamma, const float *__restrict__ saved, float *__restrict__ dgamma,
                        float *__restrict__ dbeta, float *__restrict__ coef) {
+    pdl_trigger();
+    pdl_wait();
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int ch = blockIdx.x * kWarps + warp;
     if (ch >= c) return;
@@ -497,22 +519,25 @@ int fwd_train_impl(const void *x_, const void *z_, void *y_, uint8_t *mask, cons
             auto k = bn_stats_pipe_kernel<T, VEC>;
             cudaError_t e = allow_smem(k, ps.smem);
             if (e != cudaSuccess) return (int)e;
-            k<<<g.nchunk, kThreads, ps.smem, st>>>(x, w.partial, m, c, g.txl, g.nchunk, g.rpc, g_bn_stats_reverse,
-                                                   ps.stages);
-            B200_CHECK_LAUNCH();
+            e = launch(k, g.nchunk, ps.smem, st, false, x, w.partial, m, c, g.txl, g.nchunk, g.rpc, g_bn_stats_reverse,
+                       ps.stages);
+            if (e != cudaSuccess) return (int)e;
         }
-        bn_fwd_finalize_kernel<<<(c + kWarps - 1) / kWarps, kThreads, 0, st>>>(w.partial, g.nchunk, g.rpc, m, c, gamma,
-                                                                              beta, rm, rv, nbt, saved, eps, momentum);
-        B200_CHECK_LAUNCH();
+        {
+            cudaError_t e = launch(bn_fwd_finalize_kernel, (c + kWarps - 1) / kWarps, 0, st, true, w.partial, g.nchunk,
+                                   g.rpc, m, c, gamma, beta, rm, rv, nbt, saved, eps, momentum);
+            if (e != cudaSuccess) return (int)e;
+        }
 #define B200_APPLY_PIPE(ACT, NT)                                                                                  \
     do {                                                                                                          \
         auto k = bn_apply_pipe_kernel<T, VEC, ACT, false>;                                                        \
         const PipeGeom pa = make_geom_pipe(m, c, VEC, sizeof(T), NT, false, 0);                                   \
         cudaError_t e = allow_smem(k, pa.smem);                                                                   \
         if (e != cudaSuccess) return (int)e;                                                                      \
-        k<<<pa.g.nchunk, kThreads, pa.smem, st>>>(x, z, y, mask, saved, nullptr, nullptr, nullptr, nullptr, eps, m, \
-                                                  c, pa.g.txl, pa.g.nchunk, pa.g.rpc, g_bn_apply_reverse,         \
-                                                  pa.stages);                                                     \
+        e = launch(k, pa.g.nchunk, pa.smem, st, true, x, z, y, mask, (const float *)saved, (const float *)nullptr,  \
+                   (const float *)nullptr, (const float *)nullptr, (const float *)nullptr, eps, m, c, pa.g.txl,   \
+                   pa.g.nchunk, pa.g.rpc, g_bn_apply_reverse, pa.stages);                                         \
+        if (e != cudaSuccess) return (int)e;                                                                      \
     } while (0)
         if (act == B200_ACT_NONE) B200_APPLY_PIPE(B200_ACT_NONE, 1);
         else if (act == B200_ACT_RELU) B200_APPLY_PIPE(B200_ACT_RELU, 1);
@@ -609,15 +634,15 @@ int bwd_impl(const void *dy_, const void *dy2_, const void *x_, const uint8_t *m
         cudaError_t e = allow_smem(kr, pr.smem);                                                                  \
         if (e == cudaSuccess) e = allow_smem(ka, pa.smem);                                                        \
         if (e != cudaSuccess) return (int)e;                                                                      \
-        kr<<<g.nchunk, kThreads, pr.smem, st>>>(dy, dy2, x, mask, saved, w.partial, m, c, g.txl, g.nchunk, g.rpc, \
-                                                g_bn_stats_reverse, pr.stages);                                   \
-        B200_CHECK_LAUNCH();                                                                                      \
-        bn_bwd_finalize_kernel<<<(c + kWarps - 1) / kWarps, kThreads, 0, st>>>(w.partial, g.nchunk, m, c, gamma,   \
-                                                                              saved, dgamma, dbeta, w.coef);     \
-        B200_CHECK_LAUNCH();                                                                                      \
-        ka<<<pa.g.nchunk, kThreads, pa.smem, st>>>(dy, dy2, x, mask, saved, w.coef, dx, dz, m, c, pa.g.txl,       \
-                                                   pa.g.nchunk, pa.g.rpc, g_bn_apply_reverse, pa.stages);         \
-        B200_CHECK_LAUNCH();                                                                                      \
+        e = launch(kr, g.nchunk, pr.smem, st, false, dy, dy2, x, mask, saved, w.partial, m, c, g.txl, g.nchunk,   \
+                   g.rpc, g_bn_stats_reverse, pr.stages);                                                         \
+        if (e != cudaSuccess) return (int)e;                                                                      \
+        e = launch(bn_bwd_finalize_kernel, (c + kWarps - 1) / kWarps, 0, st, true, w.partial, g.nchunk, m, c,     \
+                   gamma, saved, dgamma, dbeta, w.coef);                                                          \
+        if (e != cudaSuccess) return (int)e;                                                                      \
+        e = launch(ka, pa.g.nchunk, pa.smem, st, true, dy, dy2, x, mask, saved, (const float *)w.coef, dx, dz, m, \
+                   c, pa.g.txl, pa.g.nchunk, pa.g.rpc, g_bn_apply_reverse, pa.stages);                            \
+        if (e != cudaSuccess) return (int)e;                                                                      \
     } while (0)
         if (act == B200_ACT_NONE) B200_BWD_PIPE(B200_ACT_NONE);
         else if (act == B200_ACT_RELU) B200_BWD_PIPE(B200_ACT_RELU);
@@ -671,6 +696,7 @@ extern "C" int b200_tune_set(const char *key, int value) {
     if (eq("bn_stats_reverse")) { g_bn_stats_reverse = value != 0; return 0; }
     if (eq("bn_apply_reverse")) { g_bn_apply_reverse = value != 0; return 0; }
     if (eq("bn_pipeline")) { g_bn_pipeline = value != 0; return 0; }
+    if (eq("bn_pdl")) { g_bn_pdl = value != 0; return 0; }
     if (eq("bn_pipe_stages")) { if (value < 0 || value > kMaxStages || value == 1) return (int)cudaErrorInvalidValue; g_bn_pipe_stages = value; return 0; }
     if (eq("bn_pipe_ctas_per_sm")) { if (value < 1 || value > 8) return (int)cudaErrorInvalidValue; g_bn_pipe_ctas_per_sm = value; return 0; }
     return (int)cudaErrorInvalidValue;

@@ -47,6 +47,13 @@ __device__ __forceinline__ void bulk_g2s(void *dst, const void *src, uint32_t by
                  "l"(src), "r"(bytes), "r"(smem_u32(bar))
                  : "memory");
 }
+// Programmatic dependent launch: a kernel launched with the programmatic-stream-serialization attribute
+// may start (be scheduled, run its prologue, prefetch inputs that older kernels produced) while its
+// predecessor drains; pdl_wait() blocks until the predecessor has completed and its writes are visible.
+// Both are no-ops for ordinary launches.
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+
 __device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 __device__ __forceinline__ void fence_mbar_init() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
 
@@ -140,6 +147,7 @@ bn_stats_pipe_kernel(const T *__restrict__ x, float2 *__restrict__ partial, int6
                      int64_t rpc, int reverse, int nstages) {
     extern __shared__ __align__(128) unsigned char dyn_smem[];
     __shared__ float red[kWarps * 32 * 2 * VEC];
+    pdl_trigger();
     const int tx = 1 << txl;
     const int txi = threadIdx.x & (tx - 1);
     const int cv = c / VEC;
@@ -207,7 +215,8 @@ bn_apply_pipe_kernel(const T *__restrict__ x, const T *__restrict__ z, T *__rest
     ring.src[0] = reinterpret_cast<const unsigned char *>(x);
     if (NT == 2) ring.src[NT - 1] = reinterpret_cast<const unsigned char *>(z);
     ring.msrc = nullptr;
-    ring.setup(dyn_smem, txl, nstages, (int64_t)c * sizeof(T), r0, r1);
+    ring.setup(dyn_smem, txl, nstages, (int64_t)c * sizeof(T), r0, r1);  // x (and z) tiles are already in flight ...
+    if (!EVAL) pdl_wait();                                               // ... before the statistics are final
     float sc[VEC], sf[VEC];
 #pragma unroll
     for (int k = 0; k < VEC; ++k) {
@@ -264,6 +273,7 @@ bn_bwd_reduce_pipe_kernel(const T *__restrict__ dy, const T *__restrict__ dy2, c
                           int nchunk, int64_t rpc, int reverse, int nstages) {
     extern __shared__ __align__(128) unsigned char dyn_smem[];
     __shared__ float red[kWarps * 32 * 2 * VEC];
+    pdl_trigger();
     constexpr bool MASK = (ACT == B200_ACT_ADD_RELU);
     const int tx = 1 << txl;
     const int txi = threadIdx.x & (tx - 1);
@@ -351,7 +361,8 @@ bn_bwd_apply_pipe_kernel(const T *__restrict__ dy, const T *__restrict__ dy2, co
     ring.src[1] = reinterpret_cast<const unsigned char *>(x);
     if (DY2) ring.src[NT - 1] = reinterpret_cast<const unsigned char *>(dy2);
     ring.msrc = mask;
-    ring.setup(dyn_smem, txl, nstages, (int64_t)c * sizeof(T), r0, r1);
+    ring.setup(dyn_smem, txl, nstages, (int64_t)c * sizeof(T), r0, r1);  // dy / x tiles in flight ...
+    pdl_wait();                                                          // ... before the coefficients exist
     float mean[VEC], c0[VEC], c1[VEC], c2[VEC], sc[VEC], sf[VEC];
 #pragma unroll
     for (int k = 0; k < VEC; ++k) {

@@ -46,6 +46,8 @@ const char *b200_error_string(int code);
  *   "bn_pipeline"      1 = bulk-async (cp.async.bulk + mbarrier) shared-memory ring kernels where the
  *                      shape allows (16-byte vectors, power-of-two C/vec), 0 = direct-load kernels
  *   "bn_pipe_ctas_per_sm" resident CTAs per SM the bulk-async grid is sized for (default 2)
+ *   "bn_pdl"           1 = the finalize/apply kernels of the bulk-async path are launched with programmatic
+ *                      dependent launch (they start while their predecessor drains), default 1
  *   "bn_pipe_stages"   shared-memory ring depth of the bulk-async kernels, 2..8 (default 0 = automatic)
  * Returns cudaErrorInvalidValue for an unknown key or value. */
 int b200_tune_set(const char *key, int value);

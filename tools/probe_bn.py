@@ -12,7 +12,7 @@ from imagent_distributed_training_pytorch_with_slurm_b200 import _cabi as cabi  
 
 dev = "cuda"
 flush = torch.empty(512 << 20, dtype=torch.uint8, device=dev)
-SHAPES = [(256, 64, 112, 112), (256, 256, 56, 56), (256, 64, 56, 56), (256, 128, 28, 28), (256, 1024, 14, 14),
+SHAPES = [(256, 64, 112, 112), (256, 64, 56, 56), (256, 128, 28, 28), (256, 256, 14, 14), (256, 1024, 14, 14),
           (256, 2048, 7, 7), (256, 512, 7, 7)]
 
 
@@ -32,7 +32,7 @@ def timeit(fn, reps=5):
 
 def main():
     # (vec, direct-kernel CTAs, reverse, pipeline, pipeline CTAs/SM)
-    knobs = [(8, 1184, 1, 0, 3), (8, 1184, 1, 1, 1), (8, 1184, 1, 1, 2), (8, 1184, 1, 1, 3)]
+    knobs = [(8, 1184, 1, 1, 2, 0), (8, 1184, 1, 1, 2, 1)]
     res = []
     for shape in SHAPES:
         n, c, h, w = shape
@@ -42,13 +42,14 @@ def main():
         g, b = torch.ones(c, device=dev), torch.zeros(c, device=dev)
         rm, rv = torch.zeros(c, device=dev), torch.ones(c, device=dev)
         e = x.numel() * 2
-        for vec, ctas, rev, pipe, pctas in knobs:
+        for vec, ctas, rev, pipe, pctas, pdl in knobs:
+            cabi.tune_set("bn_pdl", pdl)
             cabi.tune_set("bn_vec_bf16", vec)
             cabi.tune_set("bn_target_ctas", ctas)
             cabi.tune_set("bn_stats_reverse", rev)
             cabi.tune_set("bn_pipeline", pipe)
             cabi.tune_set("bn_pipe_ctas_per_sm", pctas)
-            row = {"shape": shape, "vec": vec, "ctas": ctas, "rev": rev, "pipe": pipe, "pctas": pctas}
+            row = {"shape": shape, "vec": vec, "ctas": ctas, "rev": rev, "pipe": pipe, "pctas": pctas, "pdl": pdl}
             for act, name in ((1, "relu"), (2, "add_relu")):
                 zz = z if act == 2 else None
                 _, saved, mask = cabi.bn_fwd_train(x, zz, g, b, rm, rv, None, 1e-5, 0.1, act)
