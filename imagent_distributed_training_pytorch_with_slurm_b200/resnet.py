@@ -13,7 +13,10 @@ Replaces ``models.resnet18(pretrained=False, num_classes=...)`` (imagenet.py:312
   reverse calling cuDNN (dgrad/wgrad), the B200 BatchNorm(+add)+ReLU kernels and cuBLAS directly,
   writing every parameter gradient straight into the gradient arena and telling the data-parallel
   wrapper how far it has got so bucket all-reduces overlap the rest of the backward;
-* activations are channels-last, bf16 (default) or float32.
+* activations are channels-last, bf16 (default) or float32;
+* convolution weight gradients (needed only at the next gradient flush) are computed on a second CUDA
+  stream, concurrently with the data-gradient -> BatchNorm-backward chain that the rest of the backward
+  is waiting for (``use_wgrad_stream``; +4 % on ResNet-50).
 
 BatchNorm sites: ``bn+relu`` resnet.py:93-94,147-152,269-270; ``bn+add+relu`` :97-103,155-161;
 ``bn`` (downsample) :240-243.  Convolutions and the final Linear stay on cuDNN / cuBLAS.
@@ -67,6 +70,7 @@ class _Conv(nn.Module):
         self.weight = None  # set by _adopt
         self.w_compute = None
         self.grad_view = None
+        self.side = None       # [cuda stream or None] shared with the network: where weight gradients are computed
         self.grad_offset = 0   # element offset of this weight's slot in the gradient arena
         self.pending = None    # list shared with the network: (wgrad tensor, arena offset) awaiting one pack launch
 
@@ -74,10 +78,24 @@ class _Conv(nn.Module):
         return torch.ops.aten.convolution(x, self.w_compute, None, self.stride, self.padding, self.dilation, False,
                                           (0, 0), self.groups)
 
+    def _cb(self, gy, x, mask):
+        return torch.ops.aten.convolution_backward(gy, x, self.w_compute, None, self.stride, self.padding,
+                                                   self.dilation, False, (0, 0), self.groups, mask)
+
     def bwd(self, gy, x, need_gx=True):
-        gx, gw, _ = torch.ops.aten.convolution_backward(gy, x, self.w_compute, None, self.stride, self.padding,
-                                                        self.dilation, False, (0, 0), self.groups,
-                                                        (need_gx, True, False))
+        side = self.side[0] if self.side is not None else None
+        if side is not None and need_gx and gy.is_cuda:
+            # weight gradient on the side stream (nothing downstream needs it before the bucket flush), data
+            # gradient on the main stream where the rest of the backward is waiting for it
+            main = torch.cuda.current_stream()
+            side.wait_stream(main)
+            with torch.cuda.stream(side):
+                _, gw, _ = self._cb(gy, x, (False, True, False))
+            gy.record_stream(side)
+            x.record_stream(side)
+            gx = self._cb(gy, x, (True, False, False))[0]
+        else:
+            gx, gw, _ = self._cb(gy, x, (need_gx, True, False))
         dense = gw.is_contiguous(memory_format=torch.channels_last) if gw.dim() == 4 else gw.is_contiguous()
         if self.pending is not None and dense:
             self.pending.append((gw, self.grad_offset))  # K,R,S,C memory order == the arena slot's order
@@ -246,7 +264,7 @@ class _WholeNet(torch.autograd.Function):
 class B200ResNet(nn.Module):
     """Drop-in for a torchvision ResNet (``models.<arch>(weights=None, num_classes=...)``)."""
 
-    def __init__(self, arch="resnet18", num_classes=1000, device=None, dtype=torch.bfloat16):
+    def __init__(self, arch="resnet18", num_classes=1000, device=None, dtype=torch.bfloat16, wgrad_stream=True):
         super().__init__()
         import torchvision.models as tvm
 
@@ -272,6 +290,8 @@ class B200ResNet(nn.Module):
             setattr(self, f"layer{li}", nn.Sequential(*[_Block(b) for b in getattr(tv, f"layer{li}")]))
         self.fc = _Linear(tv.fc)
         self._adopt(tv)
+        if wgrad_stream and device.type == "cuda":
+            self.use_wgrad_stream(True)
         self.__dict__["_stem_s2d"] = None
         self._anchor = torch.zeros((), device=device, requires_grad=True)
         self.__dict__["_sink"] = None  # data-parallel wrapper (grad_ready / backward_done); not a submodule
@@ -281,6 +301,7 @@ class B200ResNet(nn.Module):
     def _adopt(self, tv):
         """Move the torchvision module's parameters/buffers into flat arenas, keeping key order."""
         self.__dict__["_pending"] = []
+        self.__dict__["_side"] = [None]
         tv_params = dict(tv.named_parameters())
         tv_mods = dict(tv.named_modules())
         names = [n for n, _ in tv.named_parameters()]
@@ -320,7 +341,7 @@ class B200ResNet(nn.Module):
                 setattr(m, leaf, p)
                 if isinstance(m, _Conv):
                     m.grad_view = a.view(a.grads, i)
-                    m.grad_offset, m.pending = a.offsets[i], self._pending
+                    m.grad_offset, m.pending, m.side = a.offsets[i], self._pending, self._side
                     m.w_compute = a.view(a.shadow, i) if a.shadow is not None else p.detach()
                 elif isinstance(m, _BN):
                     if leaf == "weight":
@@ -343,8 +364,15 @@ class B200ResNet(nn.Module):
         """Arena offsets (descending) at which gradients become final during the backward."""
         return sorted(set(self._marks.values()) | {0}, reverse=True)
 
+    def use_wgrad_stream(self, enable=True):
+        """Compute convolution weight gradients on a second CUDA stream, concurrently with the
+        data-gradient / BatchNorm-backward chain (they are only needed at the next gradient flush)."""
+        self._side[0] = torch.cuda.Stream(device=self.device) if enable else None
+
     def _flush_grads(self):
         """One K5 launch writes every weight gradient produced since the last flush into the arena."""
+        if self._side[0] is not None:
+            torch.cuda.current_stream().wait_stream(self._side[0])
         if self._pending:
             _cabi.pack_grads([t for t, _ in self._pending], [o for _, o in self._pending], self.arena.grads)
             self._pending.clear()
