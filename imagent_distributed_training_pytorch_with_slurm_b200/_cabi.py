@@ -39,6 +39,10 @@ SIGNATURES = {
     "b200_bn_bwd": (_i32, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _sz, _i64, _i32, _i32, _i32, _vp]),
     "b200_maxpool3x3s2_fwd": (_i32, [_vp, _vp, _vp, _i64, _i32, _i32, _i32, _i32, _vp]),
     "b200_maxpool3x3s2_bwd": (_i32, [_vp, _vp, _vp, _i64, _i32, _i32, _i32, _i32, _vp]),
+    "b200_bn_dual_supported": (_i32, [_i32, _i32]),
+    "b200_bn_stats": (_i32, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _sz, _i64, _i32, _f32, _f32, _i32, _vp]),
+    "b200_bn_fwd_train_dual": (_i32, [_vp] * 12 + [_sz, _i64, _i32, _f32, _f32, _i32, _vp]),
+    "b200_bn_bwd_dual": (_i32, [_vp] * 16 + [_sz, _i64, _i32, _i32, _vp]),
     "b200_pack_grads": (_i32, [_c.POINTER(_vp), _c.POINTER(_i64), _c.POINTER(_i64), _i32, _vp, _f32, _i32, _vp]),
     "b200_input_workspace_bytes": (_sz, [_i64, _i32, _i32, _i32, _i32]),
     "b200_input_crop_resize_flip_norm": (_i32, [_vp, _vp, _vp, _vp, _vp, _sz, _i64, _i32, _i32, _i32, _i32,
@@ -327,6 +331,68 @@ def bn_bwd(dy, x, mask, gamma, saved, act, dgamma=None, dbeta=None, dy2=None):
     stats.end("bn_bwd", 3, s, ((6 if act == ACT_ADD_RELU else 5) + (2 if dy2 is not None else 0)) * e
               + (2 * (mask.numel() - 16) if mask is not None else 0))
     return dx, dz, dgamma, dbeta
+
+
+def bn_dual_supported(x):
+    return bool(load().b200_bn_dual_supported(x.shape[1], dtype_code(x)))
+
+
+def bn_stats(x, gamma, beta, running_mean, running_var, num_batches_tracked, eps, momentum):
+    """Statistics + finalize only (no output tensor).  Returns saved float32[4,C]."""
+    _need_cuda(x, gamma, beta)
+    m, c = _rows_channels(x)
+    lib = load()
+    dt = dtype_code(x)
+    saved = torch.empty(4, c, dtype=torch.float32, device=x.device)
+    ws = workspace(x.device, lib.b200_bn_workspace_bytes(m, c, dt), "bn")
+    s = stats.begin("bn_fwd")
+    _check(lib.b200_bn_stats(_ptr(x), _ptr(gamma), _ptr(beta), _ptr(running_mean), _ptr(running_var),
+                             _ptr(num_batches_tracked), _ptr(saved), _ptr(ws), ws.numel(), m, c, eps, momentum, dt,
+                             _stream()), "b200_bn_stats")
+    stats.end("bn_fwd", 2, s, m * c * x.element_size())
+    return saved
+
+
+def bn_fwd_train_dual(x, x2, saved2, gamma, beta, running_mean, running_var, num_batches_tracked, eps, momentum):
+    """y = relu(bn(x) + x2*saved2.scale + saved2.shift).  Returns (y, saved, mask).  Check
+    ``bn_dual_supported`` first; unsupported shapes raise."""
+    _need_cuda(x, x2, saved2, gamma, beta)
+    m, c = _rows_channels(x)
+    if x2.shape != x.shape or x2.dtype != x.dtype:
+        raise B200Error("x2 must match x")
+    _rows_channels(x2)
+    lib = load()
+    dt = dtype_code(x)
+    y = torch.empty_like(x)
+    saved = torch.empty(4, c, dtype=torch.float32, device=x.device)
+    mask = torch.empty(m * (c // lib.b200_bn_vec(dt)) + 16, dtype=torch.uint8, device=x.device)
+    ws = workspace(x.device, lib.b200_bn_workspace_bytes(m, c, dt), "bn")
+    s = stats.begin("bn_fwd")
+    rc = lib.b200_bn_fwd_train_dual(_ptr(x), _ptr(x2), _ptr(y), _ptr(mask), _ptr(gamma), _ptr(beta), _ptr(running_mean),
+                                    _ptr(running_var), _ptr(num_batches_tracked), _ptr(saved), _ptr(saved2), _ptr(ws),
+                                    ws.numel(), m, c, eps, momentum, dt, _stream())
+    _check(rc, "b200_bn_fwd_train_dual")
+    stats.end("bn_fwd", 3, s, 4 * m * c * x.element_size() + mask.numel() - 16)
+    return y, saved, mask
+
+
+def bn_bwd_dual(dy, dy2, x, x2, mask, gamma, gamma2, saved, saved2, dgamma, dbeta, dgamma2, dbeta2):
+    """Backward of ``bn_fwd_train_dual``.  Returns (dx, dx2)."""
+    _need_cuda(dy, dy2, x, x2, mask, gamma, gamma2, saved, saved2)
+    m, c = _rows_channels(x)
+    _rows_channels(dy)
+    lib = load()
+    dt = dtype_code(x)
+    dx, dx2 = torch.empty_like(x), torch.empty_like(x2)
+    ws = workspace(x.device, lib.b200_bn_workspace_bytes(m, c, dt), "bn")
+    s = stats.begin("bn_bwd")
+    rc = lib.b200_bn_bwd_dual(_ptr(dy), _ptr(dy2), _ptr(x), _ptr(x2), _ptr(mask), _ptr(gamma), _ptr(gamma2), _ptr(saved),
+                              _ptr(saved2), _ptr(dx), _ptr(dx2), _ptr(dgamma), _ptr(dbeta), _ptr(dgamma2), _ptr(dbeta2),
+                              _ptr(ws), ws.numel(), m, c, dt, _stream())
+    _check(rc, "b200_bn_bwd_dual")
+    e = m * c * x.element_size()
+    stats.end("bn_bwd", 3, s, (8 + (2 if dy2 is not None else 0)) * e + 2 * (mask.numel() - 16))
+    return dx, dx2
 
 
 # ---- K5 -------------------------------------------------------------------------------------------

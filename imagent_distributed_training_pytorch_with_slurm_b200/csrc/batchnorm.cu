@@ -491,12 +491,13 @@ struct Ws {
     float *coef;
 };
 
-size_t ws_bytes_for(const Geom &g, int c) { return sizeof(float2) * (size_t)c * g.nchunk + sizeof(float) * 3 * (size_t)c + 64; }
+// sized for the largest user: the dual backward keeps float4 partials and two coefficient sets
+size_t ws_bytes_for(const Geom &g, int c) { return sizeof(float4) * (size_t)c * g.nchunk + sizeof(float) * 6 * (size_t)c + 64; }
 
 Ws carve(void *ws, const Geom &g, int c) {
     Ws w;
     w.partial = static_cast<float2 *>(ws);
-    size_t off = sizeof(float2) * (size_t)c * g.nchunk;
+    size_t off = sizeof(float4) * (size_t)c * g.nchunk;
     off = (off + 15) / 16 * 16;
     w.coef = reinterpret_cast<float *>(static_cast<char *>(ws) + off);
     return w;
@@ -505,7 +506,9 @@ Ws carve(void *ws, const Geom &g, int c) {
 template <typename T, int VEC>
 int fwd_train_impl(const void *x_, const void *z_, void *y_, uint8_t *mask, const float *gamma, const float *beta,
                    float *rm, float *rv, int64_t *nbt, float *saved, void *ws, size_t ws_bytes, int64_t m, int c,
-                   float eps, float momentum, int act, cudaStream_t st) {
+                   float eps, float momentum, int act, cudaStream_t st, const float *saved2 = nullptr) {
+    // y_ == nullptr: statistics + finalize only.  saved2 != nullptr: z is a raw tensor to be normalised
+    // with saved2{scale, shift} before the add (bulk-async kernels only).
     const T *x = static_cast<const T *>(x_);
     const T *z = static_cast<const T *>(z_);
     T *y = static_cast<T *>(y_);
@@ -536,9 +539,10 @@ int fwd_train_impl(const void *x_, const void *z_, void *y_, uint8_t *mask, cons
         if (e != cudaSuccess) return (int)e;                                                                      \
         e = launch(k, pa.g.nchunk, pa.smem, st, true, x, z, y, mask, (const float *)saved, (const float *)nullptr,  \
                    (const float *)nullptr, (const float *)nullptr, (const float *)nullptr, eps, m, c, pa.g.txl,   \
-                   pa.g.nchunk, pa.g.rpc, g_bn_apply_reverse, pa.stages);                                         \
+                   pa.g.nchunk, pa.g.rpc, g_bn_apply_reverse, pa.stages, saved2);                                 \
         if (e != cudaSuccess) return (int)e;                                                                      \
     } while (0)
+        if (!y) return 0;
         if (act == B200_ACT_NONE) B200_APPLY_PIPE(B200_ACT_NONE, 1);
         else if (act == B200_ACT_RELU) B200_APPLY_PIPE(B200_ACT_RELU, 1);
         else B200_APPLY_PIPE(B200_ACT_ADD_RELU, 2);
@@ -546,6 +550,7 @@ int fwd_train_impl(const void *x_, const void *z_, void *y_, uint8_t *mask, cons
         B200_CHECK_LAUNCH();
         return 0;
     }
+    if (saved2) return (int)cudaErrorNotSupported;
     const Geom g = make_geom(m, c, VEC, Unroll<T, VEC>::U);
     if (ws_bytes < ws_bytes_for(g, c)) return (int)cudaErrorInvalidValue;
     const Ws w = carve(ws, g, c);
@@ -555,6 +560,7 @@ int fwd_train_impl(const void *x_, const void *z_, void *y_, uint8_t *mask, cons
     bn_fwd_finalize_kernel<<<(c + kWarps - 1) / kWarps, kThreads, 0, st>>>(w.partial, g.nchunk, g.rpc, m, c, gamma, beta,
                                                                           rm, rv, nbt, saved, eps, momentum);
     B200_CHECK_LAUNCH();
+    if (!y) return 0;
     const int rev = g_bn_apply_reverse;
 #define B200_APPLY(ACT)                                                                                         \
     bn_apply_kernel<T, VEC, ACT, false><<<grid, kThreads, 0, st>>>(x, z, y, mask, saved, nullptr, nullptr, nullptr, \
@@ -581,7 +587,7 @@ int fwd_eval_impl(const void *x_, const void *z_, void *y_, const float *gamma, 
         cudaError_t e = allow_smem(k, pa.smem);                                                                   \
         if (e != cudaSuccess) return (int)e;                                                                      \
         k<<<pa.g.nchunk, kThreads, pa.smem, st>>>(x, z, y, nullptr, nullptr, gamma, beta, rm, rv, eps, m, c,      \
-                                                  pa.g.txl, pa.g.nchunk, pa.g.rpc, 0, pa.stages);                 \
+                                                  pa.g.txl, pa.g.nchunk, pa.g.rpc, 0, pa.stages, nullptr);        \
     } while (0)
         if (act == B200_ACT_NONE) B200_APPLY_PIPE(B200_ACT_NONE, 1);
         else if (act == B200_ACT_RELU) B200_APPLY_PIPE(B200_ACT_RELU, 1);
@@ -674,6 +680,49 @@ int bwd_impl(const void *dy_, const void *dy2_, const void *x_, const uint8_t *m
     else B200_BWD(B200_ACT_ADD_RELU);
 #undef B200_BWD
     return 0;
+}
+
+template <typename T, int VEC>
+int bwd_dual_impl(const void *dy_, const void *dy2_, const void *x_, const void *x2_, const uint8_t *mask,
+                  const float *gamma, const float *gamma2, const float *saved, const float *saved2, void *dx_, void *dx2_,
+                  float *dgamma, float *dbeta, float *dgamma2, float *dbeta2, void *ws, size_t ws_bytes, int64_t m, int c,
+                  cudaStream_t st) {
+    if constexpr (VEC * sizeof(T) == 16) if (pipe_eligible(c, VEC, sizeof(T))) {
+        const T *dy = static_cast<const T *>(dy_), *dy2 = static_cast<const T *>(dy2_);
+        const T *x = static_cast<const T *>(x_), *x2 = static_cast<const T *>(x2_);
+        T *dx = static_cast<T *>(dx_), *dx2 = static_cast<T *>(dx2_);
+        if (b200_misaligned(mask)) return (int)cudaErrorMisalignedAddress;
+        const int nt = dy2 ? 4 : 3;
+        const PipeGeom pr = make_geom_pipe(m, c, VEC, sizeof(T), nt, true, sizeof(float) * kThreads * 3 * VEC);
+        const PipeGeom pa = make_geom_pipe(m, c, VEC, sizeof(T), nt, true, 0);
+        const Geom &g = pr.g;
+        if (ws_bytes < ws_bytes_for(g, c)) return (int)cudaErrorInvalidValue;
+        const Ws w = carve(ws, g, c);
+        float4 *partial = reinterpret_cast<float4 *>(w.partial);
+        cudaError_t e;
+#define B200_DUAL(DY2)                                                                                            \
+    do {                                                                                                          \
+        auto kr = bn_bwd_reduce_dual_pipe_kernel<T, VEC, DY2>;                                                    \
+        auto ka = bn_bwd_apply_dual_pipe_kernel<T, VEC, DY2>;                                                     \
+        e = allow_smem(kr, pr.smem);                                                                              \
+        if (e == cudaSuccess) e = allow_smem(ka, pa.smem);                                                        \
+        if (e != cudaSuccess) return (int)e;                                                                      \
+        e = launch(kr, g.nchunk, pr.smem, st, false, dy, dy2, x, x2, mask, saved, saved2, partial, m, c, g.txl,   \
+                   g.nchunk, g.rpc, g_bn_stats_reverse, pr.stages);                                               \
+        if (e != cudaSuccess) return (int)e;                                                                      \
+        e = launch(bn_bwd_finalize_dual_kernel, (c + kWarps - 1) / kWarps, 0, st, true, (const float4 *)partial,  \
+                   g.nchunk, m, c, gamma, gamma2, saved, saved2, dgamma, dbeta, dgamma2, dbeta2, w.coef);         \
+        if (e != cudaSuccess) return (int)e;                                                                      \
+        e = launch(ka, pa.g.nchunk, pa.smem, st, true, dy, dy2, x, x2, mask, saved, saved2, (const float *)w.coef, \
+                   dx, dx2, m, c, pa.g.txl, pa.g.nchunk, pa.g.rpc, g_bn_apply_reverse, pa.stages);                \
+        if (e != cudaSuccess) return (int)e;                                                                      \
+    } while (0)
+        if (dy2) B200_DUAL(true);
+        else B200_DUAL(false);
+#undef B200_DUAL
+        return 0;
+    }
+    return (int)cudaErrorNotSupported;
 }
 
 int check_common(int64_t m, int c, int act, int dtype, int vec) {
@@ -787,4 +836,78 @@ extern "C" int b200_bn_bwd(const void *dy, const void *dy2, const void *x, const
                                           c, act, st);
     return bwd_impl<__nv_bfloat16, 4>(dy, dy2, x, mask, gamma, saved, dx, dz, dgamma, dbeta, workspace, workspace_bytes, m, c,
                                       act, st);
+}
+
+extern "C" int b200_bn_dual_supported(int c, int dtype) {
+    if (dtype != B200_F32 && dtype != B200_BF16) return 0;
+    const int vec = b200_bn_vec(dtype);
+    if (c < 1 || c % vec) return 0;
+    return pipe_eligible(c, vec, dtype == B200_F32 ? 4 : 2) ? 1 : 0;
+}
+
+extern "C" int b200_bn_stats(const void *x, const float *gamma, const float *beta, float *running_mean,
+                             float *running_var, int64_t *num_batches_tracked, float *saved, void *workspace,
+                             size_t workspace_bytes, int64_t m, int c, float eps, float momentum, int dtype,
+                             void *stream) {
+    const int vec = b200_bn_vec(dtype);
+    int e = check_common(m, c, B200_ACT_NONE, dtype, vec);
+    if (e) return e;
+    if (m < 2 || !x || !gamma || !beta || !saved || !workspace) return (int)cudaErrorInvalidValue;
+    if (b200_misaligned(x) || b200_misaligned(workspace)) return (int)cudaErrorMisalignedAddress;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    if (dtype == B200_F32)
+        return fwd_train_impl<float, 4>(x, nullptr, nullptr, nullptr, gamma, beta, running_mean, running_var,
+                                        num_batches_tracked, saved, workspace, workspace_bytes, m, c, eps, momentum,
+                                        B200_ACT_NONE, st);
+    if (vec == 8)
+        return fwd_train_impl<__nv_bfloat16, 8>(x, nullptr, nullptr, nullptr, gamma, beta, running_mean, running_var,
+                                                num_batches_tracked, saved, workspace, workspace_bytes, m, c, eps,
+                                                momentum, B200_ACT_NONE, st);
+    return fwd_train_impl<__nv_bfloat16, 4>(x, nullptr, nullptr, nullptr, gamma, beta, running_mean, running_var,
+                                            num_batches_tracked, saved, workspace, workspace_bytes, m, c, eps, momentum,
+                                            B200_ACT_NONE, st);
+}
+
+extern "C" int b200_bn_fwd_train_dual(const void *x, const void *x2, void *y, uint8_t *mask, const float *gamma,
+                                      const float *beta, float *running_mean, float *running_var,
+                                      int64_t *num_batches_tracked, float *saved, const float *saved2, void *workspace,
+                                      size_t workspace_bytes, int64_t m, int c, float eps, float momentum, int dtype,
+                                      void *stream) {
+    const int vec = b200_bn_vec(dtype);
+    int e = check_common(m, c, B200_ACT_ADD_RELU, dtype, vec);
+    if (e) return e;
+    if (m < 2 || !x || !x2 || !y || !gamma || !beta || !saved || !saved2 || !workspace) return (int)cudaErrorInvalidValue;
+    if (b200_misaligned(x) || b200_misaligned(x2) || b200_misaligned(y) || b200_misaligned(workspace))
+        return (int)cudaErrorMisalignedAddress;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    if (dtype == B200_F32)
+        return fwd_train_impl<float, 4>(x, x2, y, mask, gamma, beta, running_mean, running_var, num_batches_tracked, saved,
+                                        workspace, workspace_bytes, m, c, eps, momentum, B200_ACT_ADD_RELU, st, saved2);
+    if (vec == 8)
+        return fwd_train_impl<__nv_bfloat16, 8>(x, x2, y, mask, gamma, beta, running_mean, running_var,
+                                                num_batches_tracked, saved, workspace, workspace_bytes, m, c, eps,
+                                                momentum, B200_ACT_ADD_RELU, st, saved2);
+    return (int)cudaErrorNotSupported;
+}
+
+extern "C" int b200_bn_bwd_dual(const void *dy, const void *dy2, const void *x, const void *x2, const uint8_t *mask,
+                                const float *gamma, const float *gamma2, const float *saved, const float *saved2,
+                                void *dx, void *dx2, float *dgamma, float *dbeta, float *dgamma2, float *dbeta2,
+                                void *workspace, size_t workspace_bytes, int64_t m, int c, int dtype, void *stream) {
+    const int vec = b200_bn_vec(dtype);
+    int e = check_common(m, c, B200_ACT_ADD_RELU, dtype, vec);
+    if (e) return e;
+    if (!dy || !x || !x2 || !mask || !gamma || !gamma2 || !saved || !saved2 || !dx || !dx2 || !workspace)
+        return (int)cudaErrorInvalidValue;
+    if (b200_misaligned(dy) || b200_misaligned(dy2) || b200_misaligned(x) || b200_misaligned(x2) || b200_misaligned(dx) ||
+        b200_misaligned(dx2) || b200_misaligned(workspace))
+        return (int)cudaErrorMisalignedAddress;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    if (dtype == B200_F32)
+        return bwd_dual_impl<float, 4>(dy, dy2, x, x2, mask, gamma, gamma2, saved, saved2, dx, dx2, dgamma, dbeta, dgamma2,
+                                       dbeta2, workspace, workspace_bytes, m, c, st);
+    if (vec == 8)
+        return bwd_dual_impl<__nv_bfloat16, 8>(dy, dy2, x, x2, mask, gamma, gamma2, saved, saved2, dx, dx2, dgamma, dbeta,
+                                               dgamma2, dbeta2, workspace, workspace_bytes, m, c, st);
+    return (int)cudaErrorNotSupported;
 }

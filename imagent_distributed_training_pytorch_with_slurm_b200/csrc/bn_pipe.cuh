@@ -201,7 +201,9 @@ __global__ void __launch_bounds__(kThreads)
 bn_apply_pipe_kernel(const T *__restrict__ x, const T *__restrict__ z, T *__restrict__ y, uint8_t *__restrict__ mask,
                      const float *__restrict__ saved, const float *__restrict__ gamma, const float *__restrict__ beta,
                      const float *__restrict__ rmean, const float *__restrict__ rvar, float eps, int64_t m, int c,
-                     int txl, int nchunk, int64_t rpc, int reverse, int nstages) {
+                     int txl, int nchunk, int64_t rpc, int reverse, int nstages, const float *__restrict__ saved2) {
+    // saved2 != nullptr (ADD_RELU only): z is the RAW output of the downsample convolution and is
+    // normalised here with the downsample BatchNorm's {scale, shift} before the add ("dual" form)
     extern __shared__ __align__(128) unsigned char dyn_smem[];
     constexpr int NT = (ACT == B200_ACT_ADD_RELU) ? 2 : 1;
     const int tx = 1 << txl;
@@ -217,7 +219,8 @@ bn_apply_pipe_kernel(const T *__restrict__ x, const T *__restrict__ z, T *__rest
     ring.msrc = nullptr;
     ring.setup(dyn_smem, txl, nstages, (int64_t)c * sizeof(T), r0, r1);  // x (and z) tiles are already in flight ...
     if (!EVAL) pdl_wait();                                               // ... before the statistics are final
-    float sc[VEC], sf[VEC];
+    float sc[VEC], sf[VEC], sc2[VEC], sf2[VEC];
+    const bool dual = (ACT == B200_ACT_ADD_RELU) && saved2 != nullptr;
 #pragma unroll
     for (int k = 0; k < VEC; ++k) {
         const int ch = cvi * VEC + k;
@@ -229,6 +232,8 @@ bn_apply_pipe_kernel(const T *__restrict__ x, const T *__restrict__ z, T *__rest
             sc[k] = saved[2 * c + ch];
             sf[k] = saved[3 * c + ch];
         }
+        sc2[k] = dual ? saved2[2 * c + ch] : 1.f;
+        sf2[k] = dual ? saved2[3 * c + ch] : 0.f;
     }
     const int64_t coff = (int64_t)cvi * VEC;
     B200_RING_LOOP(ring, t, s, ph) {
@@ -248,7 +253,7 @@ bn_apply_pipe_kernel(const T *__restrict__ x, const T *__restrict__ z, T *__rest
 #pragma unroll
                 for (int k = 0; k < VEC; ++k) {
                     float pre = fmaf(e[k], sc[k], sf[k]);
-                    if (ACT == B200_ACT_ADD_RELU) pre += w[k];
+                    if (ACT == B200_ACT_ADD_RELU) pre += dual ? fmaf(w[k], sc2[k], sf2[k]) : w[k];
                     if (ACT != B200_ACT_NONE) {
                         bits |= (pre > 0.f ? 1u : 0u) << k;
                         pre = fmaxf(pre, 0.f);
@@ -407,6 +412,202 @@ bn_bwd_apply_pipe_kernel(const T *__restrict__ dy, const T *__restrict__ dy2, co
                 const int64_t rr = row0 + r;
                 VecIO<T, VEC>::store(dx + rr * c + coff, e);
                 if (ACT == B200_ACT_ADD_RELU) VecIO<T, VEC>::store(dz + rr * c + coff, g);
+            }
+        }
+        ring.release(t, s);
+    }
+}
+
+// ---- "dual" backward: y = relu(bn(x) + bn2(x2)) (residual block with a downsample branch) ---------
+// One reduce pass accumulates sum(g), sum(g*(x-mean)), sum(g*(x2-mean2)) with g = (dy [+dy2]) * mask;
+// one apply pass writes both dx and dx2.  Versus running the two BatchNorm backwards separately this
+// never writes nor re-reads dz (the masked gradient): 8 E instead of 11 E of traffic.
+template <typename T, int VEC, bool DY2>
+__global__ void __launch_bounds__(kThreads)
+bn_bwd_reduce_dual_pipe_kernel(const T *__restrict__ dy, const T *__restrict__ dy2, const T *__restrict__ x,
+                               const T *__restrict__ x2, const uint8_t *__restrict__ mask,
+                               const float *__restrict__ saved, const float *__restrict__ saved2,
+                               float4 *__restrict__ partial, int64_t m, int c, int txl, int nchunk, int64_t rpc,
+                               int reverse, int nstages) {
+    extern __shared__ __align__(128) unsigned char dyn_smem[];
+    __shared__ float red[kThreads * 3 * VEC];
+    pdl_trigger();
+    constexpr int NT = DY2 ? 4 : 3;
+    const int tx = 1 << txl;
+    const int cvi = threadIdx.x & (tx - 1);
+    const int chunk = reverse ? (nchunk - 1 - (int)blockIdx.x) : (int)blockIdx.x;
+    const int64_t r0 = (int64_t)chunk * rpc;
+    const int64_t r1 = (r0 + rpc < m) ? (r0 + rpc) : m;
+    TileRing<NT, true> ring;
+    ring.src[0] = reinterpret_cast<const unsigned char *>(dy);
+    ring.src[1] = reinterpret_cast<const unsigned char *>(x);
+    ring.src[2] = reinterpret_cast<const unsigned char *>(x2);
+    if (DY2) ring.src[NT - 1] = reinterpret_cast<const unsigned char *>(dy2);
+    ring.msrc = mask;
+    ring.setup(dyn_smem, txl, nstages, (int64_t)c * sizeof(T), r0, r1);
+    float mean[VEC], mean2[VEC];
+#pragma unroll
+    for (int k = 0; k < VEC; ++k) {
+        mean[k] = saved[cvi * VEC + k];
+        mean2[k] = saved2[cvi * VEC + k];
+    }
+    float acc[3 * VEC];
+#pragma unroll
+    for (int k = 0; k < 3 * VEC; ++k) acc[k] = 0.f;
+    B200_RING_LOOP(ring, t, s, ph) {
+        const int nrows = ring.wait(t, s, (uint32_t)ph);
+        const uint4 *tg = reinterpret_cast<const uint4 *>(ring.stage(s, 0));
+        const uint4 *tv = reinterpret_cast<const uint4 *>(ring.stage(s, 1));
+        const uint4 *tv2 = reinterpret_cast<const uint4 *>(ring.stage(s, 2));
+        const uint4 *tg2 = reinterpret_cast<const uint4 *>(ring.stage(s, NT - 1));
+        const unsigned char *tm = ring.mstage(s);
+#pragma unroll
+        for (int u = 0; u < kPipeU; ++u) {
+            const int v = threadIdx.x + u * kThreads;
+            if ((v >> txl) < nrows) {
+                float g[VEC], e[VEC], e2[VEC];
+                unpack16<T, VEC>(tg[v], g);
+                unpack16<T, VEC>(tv[v], e);
+                unpack16<T, VEC>(tv2[v], e2);
+                if (DY2) {
+                    float h[VEC];
+                    unpack16<T, VEC>(tg2[v], h);
+#pragma unroll
+                    for (int k = 0; k < VEC; ++k) g[k] += h[k];
+                }
+                const unsigned bits = tm[v];
+#pragma unroll
+                for (int k = 0; k < VEC; ++k) {
+                    const float gk = ((bits >> k) & 1u) ? g[k] : 0.f;
+                    acc[k] += gk;
+                    acc[VEC + k] = fmaf(gk, e[k] - mean[k], acc[VEC + k]);
+                    acc[2 * VEC + k] = fmaf(gk, e2[k] - mean2[k], acc[2 * VEC + k]);
+                }
+            }
+        }
+        ring.release(t, s);
+    }
+    cta_reduce_rows<3 * VEC>(acc, tx, red);
+    if (threadIdx.x < tx) {
+#pragma unroll
+        for (int k = 0; k < VEC; ++k)
+            partial[(int64_t)(cvi * VEC + k) * nchunk + chunk] = make_float4(acc[k], acc[VEC + k], acc[2 * VEC + k], 0.f);
+    }
+}
+
+__global__ void __launch_bounds__(kThreads)
+bn_bwd_finalize_dual_kernel(const float4 *__restrict__ partial, int nchunk, int64_t m, int c,
+                            const float *__restrict__ gamma, const float *__restrict__ gamma2,
+                            const float *__restrict__ saved, const float *__restrict__ saved2,
+                            float *__restrict__ dgamma, float *__restrict__ dbeta, float *__restrict__ dgamma2,
+                            float *__restrict__ dbeta2, float *__restrict__ coef /*[6][C]*/) {
+    pdl_trigger();
+    pdl_wait();
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int ch = blockIdx.x * kWarps + warp;
+    if (ch >= c) return;
+    const float4 *p = partial + (int64_t)ch * nchunk;
+    float a = 0.f, b = 0.f, b2 = 0.f;
+    for (int i = lane; i < nchunk; i += 32) {
+        const float4 v = p[i];
+        a += v.x;
+        b += v.y;
+        b2 += v.z;
+    }
+    a = warp_sum(a);
+    b = warp_sum(b);
+    b2 = warp_sum(b2);
+    if (lane == 0) {
+        const float inv_m = 1.0f / (float)m;
+        const float gm = a * inv_m;
+        {
+            const float invstd = saved[c + ch], gs = gamma[ch] * invstd;
+            if (dgamma) dgamma[ch] = b * invstd;
+            if (dbeta) dbeta[ch] = a;
+            coef[ch] = gs;
+            coef[c + ch] = -(b * invstd * invstd * inv_m) * gs;
+            coef[2 * c + ch] = -gm * gs;
+        }
+        {
+            const float invstd = saved2[c + ch], gs = gamma2[ch] * invstd;
+            if (dgamma2) dgamma2[ch] = b2 * invstd;
+            if (dbeta2) dbeta2[ch] = a;
+            coef[3 * c + ch] = gs;
+            coef[4 * c + ch] = -(b2 * invstd * invstd * inv_m) * gs;
+            coef[5 * c + ch] = -gm * gs;
+        }
+    }
+}
+
+template <typename T, int VEC, bool DY2>
+__global__ void __launch_bounds__(kThreads)
+bn_bwd_apply_dual_pipe_kernel(const T *__restrict__ dy, const T *__restrict__ dy2, const T *__restrict__ x,
+                              const T *__restrict__ x2, const uint8_t *__restrict__ mask,
+                              const float *__restrict__ saved, const float *__restrict__ saved2,
+                              const float *__restrict__ coef, T *__restrict__ dx, T *__restrict__ dx2, int64_t m, int c,
+                              int txl, int nchunk, int64_t rpc, int reverse, int nstages) {
+    extern __shared__ __align__(128) unsigned char dyn_smem[];
+    constexpr int NT = DY2 ? 4 : 3;
+    const int tx = 1 << txl;
+    const int cvi = threadIdx.x & (tx - 1);
+    const int chunk = reverse ? (nchunk - 1 - (int)blockIdx.x) : (int)blockIdx.x;
+    const int64_t r0 = (int64_t)chunk * rpc;
+    const int64_t r1 = (r0 + rpc < m) ? (r0 + rpc) : m;
+    TileRing<NT, true> ring;
+    ring.src[0] = reinterpret_cast<const unsigned char *>(dy);
+    ring.src[1] = reinterpret_cast<const unsigned char *>(x);
+    ring.src[2] = reinterpret_cast<const unsigned char *>(x2);
+    if (DY2) ring.src[NT - 1] = reinterpret_cast<const unsigned char *>(dy2);
+    ring.msrc = mask;
+    ring.setup(dyn_smem, txl, nstages, (int64_t)c * sizeof(T), r0, r1);
+    pdl_wait();
+    float mean[VEC], c0[VEC], c1[VEC], c2[VEC], mean2[VEC], d0[VEC], d1[VEC], d2[VEC];
+#pragma unroll
+    for (int k = 0; k < VEC; ++k) {
+        const int ch = cvi * VEC + k;
+        mean[k] = saved[ch];
+        c0[k] = coef[ch];
+        c1[k] = coef[c + ch];
+        c2[k] = coef[2 * c + ch];
+        mean2[k] = saved2[ch];
+        d0[k] = coef[3 * c + ch];
+        d1[k] = coef[4 * c + ch];
+        d2[k] = coef[5 * c + ch];
+    }
+    const int64_t coff = (int64_t)cvi * VEC;
+    B200_RING_LOOP(ring, t, s, ph) {
+        const int nrows = ring.wait(t, s, (uint32_t)ph);
+        const uint4 *tg = reinterpret_cast<const uint4 *>(ring.stage(s, 0));
+        const uint4 *tv = reinterpret_cast<const uint4 *>(ring.stage(s, 1));
+        const uint4 *tv2 = reinterpret_cast<const uint4 *>(ring.stage(s, 2));
+        const uint4 *tg2 = reinterpret_cast<const uint4 *>(ring.stage(s, NT - 1));
+        const unsigned char *tm = ring.mstage(s);
+        const int64_t row0 = r0 + (int64_t)t * ring.rows_per_tile;
+#pragma unroll
+        for (int u = 0; u < kPipeU; ++u) {
+            const int v = threadIdx.x + u * kThreads;
+            const int r = v >> txl;
+            if (r < nrows) {
+                float g[VEC], e[VEC], e2[VEC];
+                unpack16<T, VEC>(tg[v], g);
+                unpack16<T, VEC>(tv[v], e);
+                unpack16<T, VEC>(tv2[v], e2);
+                if (DY2) {
+                    float h[VEC];
+                    unpack16<T, VEC>(tg2[v], h);
+#pragma unroll
+                    for (int k = 0; k < VEC; ++k) g[k] += h[k];
+                }
+                const unsigned bits = tm[v];
+#pragma unroll
+                for (int k = 0; k < VEC; ++k) {
+                    const float gk = ((bits >> k) & 1u) ? g[k] : 0.f;
+                    e[k] = fmaf(gk, c0[k], fmaf(e[k] - mean[k], c1[k], c2[k]));
+                    e2[k] = fmaf(gk, d0[k], fmaf(e2[k] - mean2[k], d1[k], d2[k]));
+                }
+                const int64_t rr = row0 + r;
+                VecIO<T, VEC>::store(dx + rr * c + coff, e);
+                VecIO<T, VEC>::store(dx2 + rr * c + coff, e2);
             }
         }
         ring.release(t, s);

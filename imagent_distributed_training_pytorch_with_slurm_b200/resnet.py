@@ -197,13 +197,24 @@ class _Block(nn.Module):
             tape["saved"].append(saved)
         conv, bn = pairs[-1]
         t = conv.fwd(cur)
+        fused = None
         if self.downsample is not None:
+            dbn = self.downsample[1]
             td = self.downsample[0].fwd(x)
-            zd, saved_d, _ = self.downsample[1].fwd_train(td, _cabi.ACT_NONE)
-            tape["td"], tape["saved_d"] = td, saved_d
+            tape["td"] = td
+            if _cabi.bn_dual_supported(t):
+                # "dual" form: the downsample BatchNorm is only reduced to {scale, shift}; its normalised output
+                # is never written - the block's last kernel applies both BatchNorms, the add and the ReLU
+                saved_d = _cabi.bn_stats(td, dbn.weight, dbn.bias, dbn.running_mean, dbn.running_var,
+                                         dbn.num_batches_tracked, dbn.eps, dbn.momentum)
+                fused = _cabi.bn_fwd_train_dual(t, td, saved_d, bn.weight, bn.bias, bn.running_mean, bn.running_var,
+                                                bn.num_batches_tracked, bn.eps, bn.momentum)
+            else:
+                zd, saved_d, _ = dbn.fwd_train(td, _cabi.ACT_NONE)
+            tape["saved_d"], tape["dual"] = saved_d, fused is not None
         else:
             zd = x
-        out, saved, mask = bn.fwd_train(t, _cabi.ACT_ADD_RELU, zd)
+        out, saved, mask = fused if fused is not None else bn.fwd_train(t, _cabi.ACT_ADD_RELU, zd)
         tape["x"].append(t)
         tape["saved"].append(saved)
         tape["mask"] = mask
@@ -226,7 +237,15 @@ class _Block(nn.Module):
         pairs = self.convs()
         conv, bn = pairs[-1]
         g_out, g_out2 = g_out if isinstance(g_out, tuple) else (g_out, None)
-        g, g_z = bn.bwd(g_out, tape["x"].pop(), tape["saved"].pop(), tape.pop("mask"), _cabi.ACT_ADD_RELU, g_out2)
+        g_td = None
+        if tape.get("dual"):
+            dbn = self.downsample[1]
+            g, g_td = _cabi.bn_bwd_dual(g_out, g_out2, tape["x"].pop(), tape["td"], tape.pop("mask"), bn.weight, dbn.weight,
+                                        tape["saved"].pop(), tape["saved_d"], bn.g_weight, bn.g_bias, dbn.g_weight,
+                                        dbn.g_bias)
+            g_z = None
+        else:
+            g, g_z = bn.bwd(g_out, tape["x"].pop(), tape["saved"].pop(), tape.pop("mask"), _cabi.ACT_ADD_RELU, g_out2)
         del g_out, g_out2
         for conv_prev, bn_prev in reversed(pairs[:-1]):
             g = conv.bwd(g, tape["a"].pop())
@@ -235,8 +254,10 @@ class _Block(nn.Module):
         x_in = tape.pop("in")
         g = conv.bwd(g, x_in, need_gx)
         if self.downsample is not None:
-            g_td, _ = self.downsample[1].bwd(g_z, tape.pop("td"), tape.pop("saved_d"), None, _cabi.ACT_NONE)
+            if g_td is None:
+                g_td, _ = self.downsample[1].bwd(g_z, tape["td"], tape["saved_d"], None, _cabi.ACT_NONE)
             del g_z
+            tape.pop("td"), tape.pop("saved_d")
             g2 = self.downsample[0].bwd(g_td, x_in, need_gx)
         else:
             g2 = g_z

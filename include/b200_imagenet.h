@@ -162,6 +162,32 @@ int b200_bn_bwd(const void *dy, const void *dy2, const void *x, const uint8_t *m
                 void *dx, void *dz, float *dgamma, float *dbeta, void *workspace, size_t workspace_bytes,
                 int64_t m, int c, int act, int dtype, void *stream);
 
+/* "Dual" form for residual blocks whose identity branch is itself conv + BatchNorm (the downsample
+ * branch, torchvision resnet.py:97-103,155-161 with :240-243):  y = relu(bn(x) + bn2(x2)).
+ * Running the two BatchNorms separately writes the normalised identity z = bn2(x2) and reads it back,
+ * and in the backward writes the masked gradient dz and reads it back twice; the dual kernels never
+ * materialise either (forward 3 E instead of 5 E for the pair of apply passes, backward 8 E instead of 11 E).
+ *   b200_bn_stats          statistics + finalize of one BatchNorm, no output tensor (use it for bn2):
+ *                          fills saved{mean,invstd,scale,shift}, updates the running statistics
+ *   b200_bn_fwd_train_dual statistics of x, then y = relu(x*scale+shift + x2*saved2.scale+saved2.shift),
+ *                          mask as in b200_bn_fwd_train(ADD_RELU)
+ *   b200_bn_bwd_dual       g = (dy [+ dy2]) * mask;  dbeta = dbeta2 = sum g;  dgamma / dgamma2 from
+ *                          sum g*(x-mean) / sum g*(x2-mean2);  dx and dx2 by the BatchNorm backward formula
+ * Only the bulk-async kernels implement the dual forms (C/vec a power of two <= 256); other shapes return
+ * cudaErrorNotSupported and the caller uses the separate entry points. */
+int b200_bn_dual_supported(int c, int dtype); /* 1 when the dual entry points handle this channel count */
+int b200_bn_stats(const void *x, const float *gamma, const float *beta, float *running_mean, float *running_var,
+                  int64_t *num_batches_tracked, float *saved, void *workspace, size_t workspace_bytes, int64_t m, int c,
+                  float eps, float momentum, int dtype, void *stream);
+int b200_bn_fwd_train_dual(const void *x, const void *x2, void *y, uint8_t *mask, const float *gamma, const float *beta,
+                           float *running_mean, float *running_var, int64_t *num_batches_tracked, float *saved,
+                           const float *saved2, void *workspace, size_t workspace_bytes, int64_t m, int c, float eps,
+                           float momentum, int dtype, void *stream);
+int b200_bn_bwd_dual(const void *dy, const void *dy2, const void *x, const void *x2, const uint8_t *mask,
+                     const float *gamma, const float *gamma2, const float *saved, const float *saved2, void *dx,
+                     void *dx2, float *dgamma, float *dbeta, float *dgamma2, float *dbeta2, void *workspace,
+                     size_t workspace_bytes, int64_t m, int c, int dtype, void *stream);
+
 /* ------------------------------------------------------------------------------------------------
  * K1  input stage: crop box -> antialiased bilinear resize -> horizontal flip -> /255 ->
  * (x-mean)/std -> cast, from uint8 NHWC batches, one pass.

@@ -123,3 +123,25 @@ def pack_grads(tensors, offsets, dst, scale=1.0):
         n = t.numel()
         flat = t.permute(0, 2, 3, 1).reshape(-1) if t.dim() == 4 else t.reshape(-1)  # memory (K,R,S,C) order
         dst[o:o + n].copy_(flat.float() * scale)
+
+
+def bn_dual_supported(x):
+    return True
+
+
+def bn_stats(x, gamma, beta, running_mean, running_var, num_batches_tracked, eps, momentum):
+    _, saved, _ = bn_fwd_train(x, None, gamma, beta, running_mean, running_var, num_batches_tracked, eps, momentum,
+                               obn.ACT_NONE)
+    return saved
+
+
+def bn_fwd_train_dual(x, x2, saved2, gamma, beta, running_mean, running_var, num_batches_tracked, eps, momentum):
+    z = (x2.double() * saved2[2].double().view(1, -1, 1, 1) + saved2[3].double().view(1, -1, 1, 1)).to(x2.dtype)
+    return bn_fwd_train(x, z, gamma, beta, running_mean, running_var, num_batches_tracked, eps, momentum,
+                        obn.ACT_ADD_RELU)
+
+
+def bn_bwd_dual(dy, dy2, x, x2, mask, gamma, gamma2, saved, saved2, dgamma, dbeta, dgamma2, dbeta2):
+    dx, dz, _, _ = bn_bwd(dy, x, mask, gamma, saved, obn.ACT_ADD_RELU, dgamma, dbeta, dy2)
+    dx2, _, _, _ = bn_bwd(dz, x2, None, gamma2, saved2, obn.ACT_NONE, dgamma2, dbeta2)
+    return dx, dx2

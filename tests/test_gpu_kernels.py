@@ -414,3 +414,53 @@ def test_pack_grads_matches_per_tensor_copies(dtype):
         flat = t.permute(0, 2, 3, 1).reshape(-1) if t.dim() == 4 else t.reshape(-1)
         want[o:o + t.numel()] = flat.float() * 0.5
     assert torch.equal(dst, want)   # cast + power-of-two scale: exact; padding between slots untouched
+
+
+# ------------------------------------------------------------------------------------------------ K2 dual
+@pytest.mark.parametrize("m,c", [(210, 64), (4099, 256), (12544, 2048), (50176, 512)])
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("two_branches", [False, True])
+def test_bn_dual_matches_separate_kernels_and_oracle(m, c, dtype, two_branches):
+    """y = relu(bn(x) + bn2(x2)) in the fused form against (a) the oracle composed of a plain BatchNorm
+    followed by bn+add+relu, (b) the separate kernels."""
+    rng = np.random.default_rng(m + c)
+    def arr(scale=1.0, shift=0.0):
+        return (rng.standard_normal((m, c)) * scale + shift).astype(np.float32)
+    x, x2, dy, dyb = arr(1.5, 0.3), arr(0.7, -1.0), arr(), arr()
+    g1, b1 = rng.uniform(0.5, 1.5, c).astype(np.float32), (rng.standard_normal(c) * 0.3).astype(np.float32)
+    g2, b2 = rng.uniform(0.5, 1.5, c).astype(np.float32), (rng.standard_normal(c) * 0.3).astype(np.float32)
+    T = lambda a: _rows_t(a, dtype)
+    xd, x2d, dyd, dybd = T(x), T(x2), T(dy), T(dyb)
+    xs, x2s = xd.float().cpu().numpy(), x2d.float().cpu().numpy()
+    dys = dyd.float().cpu().numpy() + (dybd.float().cpu().numpy() if two_branches else 0.0)
+    dev = lambda a: torch.from_numpy(a).to(DEV)
+    zeros, ones = (lambda: torch.zeros(c, device=DEV)), (lambda: torch.ones(c, device=DEV))
+    if not cabi.bn_dual_supported(torch.empty(1, c, 1, 1, dtype=dtype)):
+        pytest.skip("outside the bulk-async kernels (C/vec > 256): the model uses the separate entry points")
+    # fused
+    saved2 = cabi.bn_stats(x2d, dev(g2), dev(b2), zeros(), ones(), None, 1e-5, 0.1)
+    y, saved, mask = cabi.bn_fwd_train_dual(xd, x2d, saved2, dev(g1), dev(b1), zeros(), ones(), None, 1e-5, 0.1)
+    dg1, db1, dg2, db2 = (torch.empty(c, device=DEV) for _ in range(4))
+    dx, dx2 = cabi.bn_bwd_dual(dyd, dybd if two_branches else None, xd, x2d, mask, dev(g1), dev(g2), saved, saved2, dg1,
+                               db1, dg2, db2)
+    # oracle
+    z_o, mean2, invstd2, _, _, _ = obn.bn_train_fwd_oracle(x2s, g2, b2, np.zeros(c), np.ones(c), act=obn.ACT_NONE)
+    y_o, mean1, invstd1, _, _, pos = obn.bn_train_fwd_oracle(xs, g1, b1, np.zeros(c), np.ones(c), act=obn.ACT_ADD_RELU,
+                                                            z=z_o)
+    dx_o, dz_o, dg1_o, db1_o = obn.bn_train_bwd_oracle(dys, xs, g1, mean1, invstd1, obn.ACT_ADD_RELU, pos)
+    dx2_o, _, dg2_o, db2_o = obn.bn_train_bwd_oracle(dz_o, x2s, g2, mean2, invstd2, obn.ACT_NONE)
+    pre = (xs.astype(np.float64) - mean1) * invstd1 * g1 + b1 + (x2s.astype(np.float64) - mean2) * invstd2 * g2 + b2
+    safe = np.abs(pre) > 1e-3
+    bf = dtype == torch.bfloat16
+    tol = (lambda ref: np.abs(ref).max() * 2 ** -7) if bf else (lambda ref: 1e-4 * (np.abs(ref).max() + 1))
+    assert np.abs(y.float().cpu().numpy() - y_o).max() <= tol(y_o)
+    assert (np.abs(dx.float().cpu().numpy() - dx_o)[safe]).max() <= tol(dx_o)
+    assert (np.abs(dx2.float().cpu().numpy() - dx2_o)[safe]).max() <= tol(dx2_o)
+    sc = np.abs(dg1_o).max() + np.abs(db1_o).max() + np.abs(dg2_o).max()
+    for got, want in ((dg1, dg1_o), (db1, db1_o), (dg2, dg2_o), (db2, db2_o)):
+        assert np.allclose(got.cpu().numpy(), want, rtol=2e-3 if bf else 1e-4, atol=(2e-3 if bf else 1e-4) * sc + 1e-3)
+    # separate kernels give the same forward output bit for bit in float32 (same fma sequence on z = bn2(x2)
+    # is not guaranteed: z is rounded to the activation dtype when materialised), so compare loosely
+    z_k, _, _ = cabi.bn_fwd_train(x2d, None, dev(g2), dev(b2), zeros(), ones(), None, 1e-5, 0.1, cabi.ACT_NONE)
+    y_k, _, _ = cabi.bn_fwd_train(xd, z_k, dev(g1), dev(b1), zeros(), ones(), None, 1e-5, 0.1, cabi.ACT_ADD_RELU)
+    assert (y.float() - y_k.float()).abs().max().item() <= tol(y_o) * 2
