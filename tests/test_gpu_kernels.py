@@ -464,3 +464,84 @@ def test_bn_dual_matches_separate_kernels_and_oracle(m, c, dtype, two_branches):
     z_k, _, _ = cabi.bn_fwd_train(x2d, None, dev(g2), dev(b2), zeros(), ones(), None, 1e-5, 0.1, cabi.ACT_NONE)
     y_k, _, _ = cabi.bn_fwd_train(xd, z_k, dev(g1), dev(b1), zeros(), ones(), None, 1e-5, 0.1, cabi.ACT_ADD_RELU)
     assert (y.float() - y_k.float()).abs().max().item() <= tol(y_o) * 2
+
+
+# ------------------------------------------------------------------------------------------------ guard bands
+def _guarded(nbytes, dev=DEV, pad=4096):
+    """A byte buffer with 0xA5 guard bands on both sides; returns (whole, start offset)."""
+    whole = torch.full((nbytes + 2 * pad,), 0xA5, dtype=torch.uint8, device=dev)
+    return whole, pad
+
+
+def _guards_intact(whole, pad, nbytes):
+    return bool((whole[:pad] == 0xA5).all()) and bool((whole[pad + nbytes:] == 0xA5).all())
+
+
+@pytest.mark.parametrize("m,c", [(4099, 64), (777, 256), (301, 2048), (50177, 8)])
+@pytest.mark.parametrize("act", [cabi.ACT_RELU, cabi.ACT_ADD_RELU])
+def test_bn_kernels_write_only_inside_their_outputs(m, c, act):
+    """compute-sanitizer is not available on the GPU pool, so out-of-bounds writes are looked for with
+    guard bands: every output of the (bulk-async) BatchNorm kernels is carved out of a larger buffer of
+    0xA5 bytes, through the raw C ABI, for ragged row counts."""
+    lib = cabi.load()
+    g = torch.Generator(device=DEV).manual_seed(m)
+    x = torch.randn(m, c, device=DEV, generator=g).to(torch.bfloat16)
+    z = torch.randn(m, c, device=DEV, generator=g).to(torch.bfloat16)
+    dy = torch.randn(m, c, device=DEV, generator=g).to(torch.bfloat16)
+    gamma, beta = torch.ones(c, device=DEV), torch.zeros(c, device=DEV)
+    rm, rv = torch.zeros(c, device=DEV), torch.ones(c, device=DEV)
+    nb = m * c * 2
+    mb = m * (c // 8) + 16
+    bufs = {k: _guarded(n) for k, n in (("y", nb), ("mask", mb), ("saved", 16 * c), ("dx", nb), ("dz", nb),
+                                         ("dg", 4 * c), ("db", 4 * c))}
+    ptr = lambda k: bufs[k][0].data_ptr() + bufs[k][1]
+    ws = torch.empty(lib.b200_bn_workspace_bytes(m, c, cabi.BF16), dtype=torch.uint8, device=DEV)
+    st = torch.cuda.current_stream().cuda_stream
+    rc = lib.b200_bn_fwd_train(x.data_ptr(), z.data_ptr() if act == 2 else None, ptr("y"), ptr("mask") if act == 2 else None,
+                               gamma.data_ptr(), beta.data_ptr(), rm.data_ptr(), rv.data_ptr(), None, ptr("saved"),
+                               ws.data_ptr(), ws.numel(), m, c, 1e-5, 0.1, act, cabi.BF16, st)
+    assert rc == 0
+    rc = lib.b200_bn_bwd(dy.data_ptr(), None, x.data_ptr(), ptr("mask") if act == 2 else None, gamma.data_ptr(),
+                         ptr("saved"), ptr("dx"), ptr("dz") if act == 2 else None, ptr("dg"), ptr("db"), ws.data_ptr(),
+                         ws.numel(), m, c, act, cabi.BF16, st)
+    assert rc == 0
+    torch.cuda.synchronize()
+    sizes = {"y": nb, "mask": mb, "saved": 16 * c, "dx": nb, "dz": nb, "dg": 4 * c, "db": 4 * c}
+    for k, (whole, pad) in bufs.items():
+        assert _guards_intact(whole, pad, sizes[k]), k
+    # and the results carved out of the guarded buffers are the ones the wrappers give
+    y2, saved2, _ = cabi.bn_fwd_train(x, z if act == 2 else None, gamma, beta, torch.zeros(c, device=DEV),
+                                      torch.ones(c, device=DEV), None, 1e-5, 0.1, act)
+    y = bufs["y"][0][4096:4096 + nb].view(torch.bfloat16).view(m, c)
+    assert torch.equal(y, y2)
+
+
+def test_maxpool_and_pack_write_only_inside_their_outputs():
+    lib = cabi.load()
+    n, c, h, w = 3, 24, 13, 9
+    oh, ow = (h - 1) // 2 + 1, (w - 1) // 2 + 1
+    g = torch.Generator(device=DEV).manual_seed(0)
+    x = torch.randn(n, h, w, c, device=DEV, generator=g).to(torch.bfloat16)
+    dy = torch.randn(n, oh, ow, c, device=DEV, generator=g).to(torch.bfloat16)
+    sizes = {"y": n * oh * ow * c * 2, "arg": n * oh * ow * c, "dx": n * h * w * c * 2}
+    bufs = {k: _guarded(v) for k, v in sizes.items()}
+    ptr = lambda k: bufs[k][0].data_ptr() + bufs[k][1]
+    st = torch.cuda.current_stream().cuda_stream
+    assert lib.b200_maxpool3x3s2_fwd(x.data_ptr(), ptr("y"), ptr("arg"), n, c, h, w, cabi.BF16, st) == 0
+    assert lib.b200_maxpool3x3s2_bwd(dy.data_ptr(), ptr("arg"), ptr("dx"), n, c, h, w, cabi.BF16, st) == 0
+    torch.cuda.synchronize()
+    for k, (whole, pad) in bufs.items():
+        assert _guards_intact(whole, pad, sizes[k]), k
+    # pack: slots separated by untouched padding
+    ts = [torch.randn(n_, device=DEV).to(torch.bfloat16) for n_ in (7, 64, 1000, 9408)]
+    offs, off = [], 32
+    for t in ts:
+        offs.append(off)
+        off += (t.numel() + 31) // 32 * 32 + 32
+    dst = torch.full((off,), -7.0, device=DEV)
+    cabi.pack_grads(ts, offs, dst)
+    touched = torch.zeros(off, dtype=torch.bool, device=DEV)
+    for t, o in zip(ts, offs):
+        touched[o:o + t.numel()] = True
+        assert torch.equal(dst[o:o + t.numel()], t.float())
+    assert bool((dst[~touched] == -7.0).all())
