@@ -29,7 +29,11 @@ def parse():
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=5)
-    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference", "eager"],
+                    help="ours | reference (the reference's step on the host cores) | eager (stock PyTorch on the GPU: "
+                         "torchvision model + DDP + nn.CrossEntropyLoss + torch.optim.SGD, the incumbent)")
+    ap.add_argument("--eager-amp", action="store_true", help="--impl eager: bf16 autocast + channels_last instead of "
+                                                             "the reference's fp32 NCHW")
     ap.add_argument("--arch", default="resnet50")
     ap.add_argument("--batch", type=int, default=256, help="images per GPU per step")
     ap.add_argument("--image", type=int, default=224)
@@ -128,6 +132,67 @@ def run_reference(a):
         "e2e": {"value": v, "unit": "images/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }))
+
+
+def run_eager(a):
+    """Stock PyTorch eager on the GPU, exactly the objects the reference builds (imagenet.py:312-325) driven by
+    its step order; reported for context only (the PyTorch-eager incumbent of SURVEY 8d)."""
+    import torch
+    import torch.distributed as dist
+    import torchvision
+
+    rank, local, world = (int(os.environ.get(k, d)) for k, d in (("RANK", "0"), ("LOCAL_RANK", "0"), ("WORLD_SIZE", "1")))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+    torch.backends.cudnn.benchmark = True
+    torch.manual_seed(0)
+    model = getattr(torchvision.models, a.arch)(weights=None, num_classes=1000).cuda()
+    if a.eager_amp:
+        model = model.to(memory_format=torch.channels_last)
+    if world > 1:
+        model = torch.nn.parallel.DistributedDataParallel(model, device_ids=[local], output_device=local)
+    crit = torch.nn.CrossEntropyLoss().cuda()
+    opt = torch.optim.SGD(model.parameters(), 0.1, momentum=0.9, weight_decay=1e-4)
+    g = torch.Generator().manual_seed(1234 + rank)
+    x = torch.randn(a.batch, 3, a.image, a.image, generator=g).to(dev)
+    if a.eager_amp:
+        x = x.contiguous(memory_format=torch.channels_last)
+    t = torch.randint(0, 1000, (a.batch,), generator=g).to(dev)
+
+    def step():
+        with torch.autocast("cuda", dtype=torch.bfloat16, enabled=a.eager_amp):
+            logits = model(x)
+            loss = crit(logits, t)
+        opt.zero_grad()
+        loss.backward()
+        opt.step()
+        _, pred = logits.topk(5, 1, True, True)  # accuracy(), imagenet.py:63-79
+        return loss
+
+    for _ in range(a.warmup):
+        step()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(a.steps):
+        loss = step()
+    e1.record()
+    torch.cuda.synchronize()
+    ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
+    if world > 1:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    if rank == 0:
+        print(json.dumps({"impl": "eager", "metric": METRIC, "value": a.batch * world * a.steps / (float(ms) / 1e3),
+                          "unit": "images/s", "n_gpus": world, "steps": a.steps, "warmup": a.warmup,
+                          "ms_per_step": float(ms) / a.steps, "higher_is_better": True, "scaling": "weak",
+                          "dtype": "bf16 autocast, channels_last" if a.eager_amp else "f32 NCHW (as the reference)",
+                          "data": "synthetic, resident float tensors (no input stage)",
+                          "config": {"workload": workload_name(a)}, "final_loss": float(loss)}))
+    if world > 1:
+        dist.destroy_process_group()
 
 
 def run_ours(a):
@@ -234,8 +299,11 @@ def run_ours(a):
     # ---- end to end through the public API with HOST buffers ------------------------------------
     e2e = None
     if not a.no_e2e:
-        wl = b200.SyntheticImageNet(a.batch, max(a.warmup, 1), a.src, a.image, rank=rank, dtype=dtype, host=True)
-        tl = b200.SyntheticImageNet(a.batch, a.steps, a.src, a.image, rank=rank, dtype=dtype, host=True)
+        fixed = os.environ.get("B200_E2E_FIXED_PARAMS", "0") == "1"  # diagnostic: skip the per-step crop draws
+        wl = b200.SyntheticImageNet(a.batch, max(a.warmup, 1), a.src, a.image, rank=rank, dtype=dtype, host=True,
+                                    fixed_params=fixed)
+        tl = b200.SyntheticImageNet(a.batch, a.steps, a.src, a.image, rank=rank, dtype=dtype, host=True,
+                                    fixed_params=fixed)
         b200.train(wl, model, crit, opt, 0, world, sync_every=1, lag=1)
         barrier()
         t0 = time.perf_counter()
@@ -295,5 +363,7 @@ if __name__ == "__main__":
     args = parse()
     if args.impl == "reference":
         run_reference(args)
+    elif args.impl == "eager":
+        run_eager(args)
     else:
         run_ours(args)

@@ -31,20 +31,45 @@ def _log_ratio32(ratio):
     return _LOG_RATIO_CACHE[key]
 
 
-def rrc_params(height, width, scale=(0.08, 1.0), ratio=(3.0 / 4.0, 4.0 / 3.0), generator=None, _scratch=None):
+class _Draw:
+    """Scalar draws from a torch CPU generator with as little Python/dispatcher overhead as possible:
+    preallocated 1-element tensors filled in place and read through numpy views.  ``uniform_`` /
+    ``random_`` on a 1-element tensor consume the generator exactly like the ``torch.empty(1).uniform_()``,
+    ``torch.randint(..., size=(1,))`` and ``torch.rand(1)`` calls torchvision makes (one 32-bit word each)."""
+
+    def __init__(self, generator):
+        self.g = generator
+        self.f = torch.empty(1, dtype=torch.float32)
+        self.i = torch.empty(1, dtype=torch.int64)
+        self.fv, self.iv = self.f.numpy(), self.i.numpy()
+
+    def uniform(self, lo, hi):
+        self.f.uniform_(lo, hi, generator=self.g)
+        return float(self.fv[0])
+
+    def exp_uniform(self, lo, hi):
+        self.f.uniform_(lo, hi, generator=self.g).exp_()
+        return float(self.fv[0])
+
+    def randint(self, n):
+        self.i.random_(0, n, generator=self.g)
+        return int(self.iv[0])
+
+
+def rrc_params(height, width, scale=(0.08, 1.0), ratio=(3.0 / 4.0, 4.0 / 3.0), generator=None, _draw=None):
     """(top, left, h, w) with the draw order and rounding of torchvision's
     ``RandomResizedCrop.get_params`` (transforms.py:928-973)."""
+    d = _draw if _draw is not None else _Draw(generator)
     area = height * width
     lo32, hi32 = _log_ratio32(ratio)
-    buf = torch.empty(1) if _scratch is None else _scratch
     for _ in range(10):
-        target_area = area * buf.uniform_(scale[0], scale[1], generator=generator).item()
-        aspect = buf.uniform_(lo32, hi32, generator=generator).exp_().item()
+        target_area = area * d.uniform(scale[0], scale[1])
+        aspect = d.exp_uniform(lo32, hi32)
         w = int(round(math.sqrt(target_area * aspect)))
         h = int(round(math.sqrt(target_area / aspect)))
         if 0 < w <= width and 0 < h <= height:
-            top = torch.randint(0, height - h + 1, size=(1,), generator=generator).item()
-            left = torch.randint(0, width - w + 1, size=(1,), generator=generator).item()
+            top = d.randint(height - h + 1)
+            left = d.randint(width - w + 1)
             return top, left, h, w
     in_ratio = float(width) / float(height)
     if in_ratio < min(ratio):
@@ -65,10 +90,10 @@ def draw_batch_params(n, height, width, generator=None, random_crop=True, flip_p
     if not random_crop:
         return (torch.tensor([[0, 0, height, width]] * n, dtype=torch.int32), torch.zeros(n, dtype=torch.uint8))
     rows, flips = [], []
-    buf = torch.empty(1)
+    d = _Draw(generator)
     for _ in range(n):
-        rows.append(rrc_params(height, width, generator=generator, _scratch=buf))
-        flips.append(1 if buf.uniform_(0.0, 1.0, generator=generator).item() < flip_p else 0)
+        rows.append(rrc_params(height, width, _draw=d))
+        flips.append(1 if d.uniform(0.0, 1.0) < flip_p else 0)
     return torch.tensor(rows, dtype=torch.int32), torch.tensor(flips, dtype=torch.uint8)
 
 
