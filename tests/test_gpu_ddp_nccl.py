@@ -1,0 +1,28 @@
+"""The data-parallel path on real GPUs over NCCL (needs >= 2 GPUs; skipped otherwise): FlatDDP + FlatSGD
+against stock DistributedDataParallel + torch.optim.SGD, same per-rank batches, float32 activations."""
+import json
+import os
+import subprocess
+import sys
+
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs")
+def test_two_gpu_nccl_matches_stock_ddp():
+    env = dict(os.environ, PYTHONPATH=ROOT)
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr",
+           "127.0.0.1", "--master-port", "29588", os.path.join(ROOT, "tests", "ddp_nccl_worker.py")]
+    r = subprocess.run(cmd, env=env, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-4000:]
+    out = json.loads([l for l in r.stdout.splitlines() if l.startswith("{")][-1])
+    assert out["keys_equal"] and out["replicas_identical"] and out["buckets"] >= 3
+    for a, b in zip(out["ours"], out["stock"]):
+        assert a == pytest.approx(b, rel=2e-3, abs=1e-6)          # epoch-average loss / top-1 / top-5
+    # updated weights after 3 steps (fp32; cuDNN's summation order differs between NHWC and NCHW)
+    assert out["global_rel_weight_diff"] < 1e-3, out
+    assert out["worst_rel_weight_diff"] < 2e-2, out
