@@ -304,10 +304,12 @@ def run_ours(a):
                                     fixed_params=fixed)
         tl = b200.SyntheticImageNet(a.batch, a.steps, a.src, a.image, rank=rank, dtype=dtype, host=True,
                                     fixed_params=fixed)
+        use_graph = world == 1 and os.environ.get("B200_E2E_GRAPH", "0") == "1"
         b200.train(wl, model, crit, opt, 0, world, sync_every=1, lag=1)
         barrier()
         t0 = time.perf_counter()
-        b200.train(tl, model, crit, opt, 0, world, sync_every=1, lag=1)  # every step: H2D of the batch, D2H of a loss
+        # every step: H2D of the batch (pinned, side stream), input kernel, the step, D2H of its loss/top-k
+        b200.train(tl, model, crit, opt, 0, world, sync_every=1, lag=1, graph=use_graph)
         barrier()
         dt = torch.tensor([time.perf_counter() - t0], device=dev)
         if world > 1:

@@ -74,6 +74,15 @@ class FlatDDP(nn.Module):
         self._works = []
         self._next = 0
 
+    def drain(self):
+        """Wait (on the stream) for every collective this wrapper has in flight."""
+        if self._buffer_work is not None:
+            self._buffer_work.wait()
+            self._buffer_work = None
+        for w in self._works:
+            w.wait()
+        self._works = []
+
     # ---- nn.Module surface ----------------------------------------------------------------------
     def forward(self, *args, **kwargs):
         if self._buffer_work is not None:
