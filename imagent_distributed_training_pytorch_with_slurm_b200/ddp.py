@@ -73,6 +73,12 @@ class FlatDDP(nn.Module):
             w.wait()  # stream-level wait: the optimizer's kernels queue behind the all-reduces
         self._works = []
         self._next = 0
+        if self._buffer_work is not None:
+            # the buffer broadcast had the whole backward to hide behind; joining it here (rather than at the
+            # next forward) keeps every collective of an iteration inside that iteration - which is also what
+            # lets the iteration be captured as one CUDA graph
+            self._buffer_work.wait()
+            self._buffer_work = None
 
     def drain(self):
         """Wait (on the stream) for every collective this wrapper has in flight."""

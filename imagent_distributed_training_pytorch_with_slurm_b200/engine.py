@@ -16,7 +16,7 @@ What changes underneath (the observable results do not):
 ``sync_every=1`` restores the reference's per-iteration synchronisation exactly; ``sync_every=1, lag=1``
 still reads every iteration's result on the host, one iteration late, so the device never waits for
 the host.  ``graph=True`` additionally replays the whole iteration (forward, loss, backward, optimizer)
-as one CUDA graph after a short eager warm-up (``_GraphedStep``).
+as one CUDA graph after a short eager warm-up (``GraphedStep``).
 """
 import time
 
@@ -125,7 +125,7 @@ class _MetricLog:
         self._collect(0)
 
 
-class _GraphedStep:
+class GraphedStep:
     """forward + loss + backward + optimizer step of one iteration as a CUDA graph.
 
     The first ``WARMUP`` iterations run eagerly (cuDNN autotuning, lazy initialisation), the next one is
@@ -135,7 +135,8 @@ class _GraphedStep:
     iteration, imagenet.py:143-147; this is the other end of that scale).  The kernels, their order and the
     side-stream / programmatic-dependent-launch structure are exactly those of the eager step, so the numbers
     are too.  Hyper-parameters are frozen into the graph: it lives for one ``train()`` call (one epoch, one
-    learning rate, imagenet.py:378-381).  An iteration with a different batch shape (the short last batch)
+    learning rate, imagenet.py:378-381) unless the caller builds a ``GraphedStep`` itself and passes it as
+    ``train(..., graph=step)`` to reuse it.  An iteration with a different batch shape (the short last batch)
     runs eagerly."""
 
     WARMUP = 3
@@ -192,10 +193,10 @@ def train(train_loader, model, criterion, optimizer, epoch, world_size, sync_eve
     model.train()
     log, iters = _MetricLog(world_size, (losses, top1, top5), sync_every, lag), 0
     if graph and world_size > 1:
-        # measured on 2 x B200 (torch 2.11, NCCL 2.28): capturing the bucket all-reduces / buffer broadcast
-        # invalidates the capture (cudaErrorStreamCaptureInvalidated); not worked around yet
+        # measured on 2 x B200 (torch 2.11, NCCL 2.28): with the bucket all-reduces / buffer broadcast inside the
+        # step the capture is invalidated (cudaErrorStreamCaptureInvalidated) and the ranks then hang in NCCL
         raise NotImplementedError("graph=True is implemented for single-process training only")
-    graphed = _GraphedStep(model, criterion, optimizer) if graph else None
+    graphed = (graph if isinstance(graph, GraphedStep) else GraphedStep(model, criterion, optimizer)) if graph else None
     start = end = time.time()
     for i, (input, target) in enumerate(train_loader):
         data_time.update(time.time() - end)
