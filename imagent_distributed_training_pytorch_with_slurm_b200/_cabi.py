@@ -161,11 +161,22 @@ class _Stats:
 stats = _Stats()
 
 _workspaces = {}
+_bn_ws_bytes = {}
+
+
+def _bn_workspace(x, m, c, dt):
+    """The shared BatchNorm scratch buffer, large enough for an [m, c] activation (size query cached)."""
+    key = (m, c, dt)
+    n = _bn_ws_bytes.get(key)
+    if n is None:
+        n = _bn_ws_bytes[key] = load().b200_bn_workspace_bytes(m, c, dt)
+    return workspace(x.device, n, "bn")
+
 
 
 def workspace(dev, nbytes, tag, zero=False):
     """Cached per-(device, tag) scratch buffer, grown on demand (PyTorch's allocator owns it)."""
-    key = (dev.index if dev.index is not None else torch.cuda.current_device(), tag)
+    key = (dev.index, tag)
     buf = _workspaces.get(key)
     if buf is None or buf.numel() < nbytes:
         n = max(int(nbytes), 256)
@@ -278,8 +289,7 @@ def bn_fwd_train(x, z, gamma, beta, running_mean, running_var, num_batches_track
         _rows_channels(z)
         # +16: the bulk-async backward fetches the mask in 16-byte units and may read past the last byte
         mask = torch.empty(m * (c // lib.b200_bn_vec(dt)) + 16, dtype=torch.uint8, device=x.device)
-    nbytes = lib.b200_bn_workspace_bytes(m, c, dt)
-    ws = workspace(x.device, nbytes, "bn")
+    ws = _bn_workspace(x, m, c, dt)
     s = stats.begin("bn_fwd")
     _check(lib.b200_bn_fwd_train(_ptr(x), _ptr(z), _ptr(y), _ptr(mask), _ptr(gamma), _ptr(beta), _ptr(running_mean),
                                  _ptr(running_var), _ptr(num_batches_tracked), _ptr(saved), _ptr(ws), ws.numel(), m, c,
@@ -322,8 +332,7 @@ def bn_bwd(dy, x, mask, gamma, saved, act, dgamma=None, dbeta=None, dy2=None):
         dgamma = torch.empty(c, dtype=torch.float32, device=x.device)
     if dbeta is None:
         dbeta = torch.empty(c, dtype=torch.float32, device=x.device)
-    nbytes = lib.b200_bn_workspace_bytes(m, c, dt)
-    ws = workspace(x.device, nbytes, "bn")
+    ws = _bn_workspace(x, m, c, dt)
     s = stats.begin("bn_bwd")
     args = (_ptr(x), _ptr(mask), _ptr(gamma), _ptr(saved), _ptr(dx), _ptr(dz), _ptr(dgamma), _ptr(dbeta), _ptr(ws),
             ws.numel(), m, c, act, dt, _stream())
@@ -351,7 +360,7 @@ def bn_stats(x, gamma, beta, running_mean, running_var, num_batches_tracked, eps
     lib = load()
     dt = dtype_code(x)
     saved = torch.empty(4, c, dtype=torch.float32, device=x.device)
-    ws = workspace(x.device, lib.b200_bn_workspace_bytes(m, c, dt), "bn")
+    ws = _bn_workspace(x, m, c, dt)
     s = stats.begin("bn_fwd")
     _check(lib.b200_bn_stats(_ptr(x), _ptr(gamma), _ptr(beta), _ptr(running_mean), _ptr(running_var),
                              _ptr(num_batches_tracked), _ptr(saved), _ptr(ws), ws.numel(), m, c, eps, momentum, dt,
@@ -373,7 +382,7 @@ def bn_fwd_train_dual(x, x2, saved2, gamma, beta, running_mean, running_var, num
     y = torch.empty_like(x)
     saved = torch.empty(4, c, dtype=torch.float32, device=x.device)
     mask = torch.empty(m * (c // lib.b200_bn_vec(dt)) + 16, dtype=torch.uint8, device=x.device)
-    ws = workspace(x.device, lib.b200_bn_workspace_bytes(m, c, dt), "bn")
+    ws = _bn_workspace(x, m, c, dt)
     s = stats.begin("bn_fwd")
     rc = lib.b200_bn_fwd_train_dual(_ptr(x), _ptr(x2), _ptr(y), _ptr(mask), _ptr(gamma), _ptr(beta), _ptr(running_mean),
                                     _ptr(running_var), _ptr(num_batches_tracked), _ptr(saved), _ptr(saved2), _ptr(ws),
@@ -391,7 +400,7 @@ def bn_bwd_dual(dy, dy2, x, x2, mask, gamma, gamma2, saved, saved2, dgamma, dbet
     lib = load()
     dt = dtype_code(x)
     dx, dx2 = torch.empty_like(x), torch.empty_like(x2)
-    ws = workspace(x.device, lib.b200_bn_workspace_bytes(m, c, dt), "bn")
+    ws = _bn_workspace(x, m, c, dt)
     s = stats.begin("bn_bwd")
     rc = lib.b200_bn_bwd_dual(_ptr(dy), _ptr(dy2), _ptr(x), _ptr(x2), _ptr(mask), _ptr(gamma), _ptr(gamma2), _ptr(saved),
                               _ptr(saved2), _ptr(dx), _ptr(dx2), _ptr(dgamma), _ptr(dbeta), _ptr(dgamma2), _ptr(dbeta2),

@@ -29,6 +29,9 @@ import torch.nn as nn
 from . import _cabi
 
 _ALIGN = 32  # floats: every parameter starts on a 128-byte boundary of the arena
+# resolved overloads: calling the packet (torch.ops.aten.convolution) re-resolves the overload on every call
+_conv = torch.ops.aten.convolution.default
+_conv_bwd = torch.ops.aten.convolution_backward.default
 
 
 class ParamArena:
@@ -75,12 +78,11 @@ class _Conv(nn.Module):
         self.pending = None    # list shared with the network: (wgrad tensor, arena offset) awaiting one pack launch
 
     def fwd(self, x):
-        return torch.ops.aten.convolution(x, self.w_compute, None, self.stride, self.padding, self.dilation, False,
-                                          (0, 0), self.groups)
+        return _conv(x, self.w_compute, None, self.stride, self.padding, self.dilation, False, (0, 0), self.groups)
 
     def _cb(self, gy, x, mask):
-        return torch.ops.aten.convolution_backward(gy, x, self.w_compute, None, self.stride, self.padding,
-                                                   self.dilation, False, (0, 0), self.groups, mask)
+        return _conv_bwd(gy, x, self.w_compute, None, self.stride, self.padding, self.dilation, False, (0, 0),
+                         self.groups, mask)
 
     def bwd(self, gy, x, need_gx=True):
         side = self.side[0] if self.side is not None else None
@@ -129,11 +131,11 @@ class _StemS2D:
         return self._w
 
     def fwd(self, x):
-        return torch.ops.aten.convolution(x, self.weight(), None, (1, 1), (0, 0), (1, 1), False, (0, 0), 1)
+        return _conv(x, self.weight(), None, (1, 1), (0, 0), (1, 1), False, (0, 0), 1)
 
     def bwd(self, gy, x):
-        _, gw, _ = torch.ops.aten.convolution_backward(gy, x, self.weight(), None, (1, 1), (0, 0), (1, 1), False,
-                                                       (0, 0), 1, (False, True, False))
+        _, gw, _ = _conv_bwd(gy, x, self.weight(), None, (1, 1), (0, 0), (1, 1), False, (0, 0), 1,
+                             (False, True, False))
         k = gw.shape[0]
         g = gw[:, :12].reshape(k, 2, 2, 3, 4, 4).permute(0, 3, 4, 1, 5, 2).reshape(k, 3, 8, 8)
         self.conv.grad_view.copy_(g[:, :, :7, :7])
