@@ -42,7 +42,7 @@ def parse():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-graph", action="store_true",
-                    help="single-GPU runs replay the step as a CUDA graph (host-independent); this keeps it eager")
+                    help="by default the step is replayed as CUDA graph(s) (host-independent); this keeps it eager")
     ap.add_argument("--ref-batch", type=int, default=16, help="bounded CPU sample: images per reference step")
     return ap.parse_args()
 
@@ -258,9 +258,25 @@ def run_ours(a):
         step(i)
     barrier()
     eager_step = step
-    graphed = world == 1 and not a.no_graph
-    launches_per_step = None
-    if graphed:
+    graphed = not a.no_graph
+    _cabi.stats.reset()
+    step(a.warmup)                       # one more eager step just to count our launches per step
+    launches_per_step = _cabi.stats.launches
+    seg_runner = None
+    if graphed and world > 1:
+        # multi-process: a chain of CUDA graphs cut at the NCCL collectives (SegmentedGraphStep); the input
+        # kernel is launched eagerly in front of it
+        seg_runner = b200.SegmentedGraphStep(model, crit, opt)
+
+        def step(i):  # noqa: F811
+            boxes, flips, tgt = params[i]
+            x = _cabi.input_stage(images, boxes, flips, a.image, a.image, mean, std, dtype, _cabi.LAYOUT_S2D_STEM)
+            return seg_runner(x, tgt)[0]
+
+        for _ in range(seg_runner.WARMUP + 2):
+            step(a.warmup)
+        barrier()
+    if graphed and world == 1:
         # The whole step as ONE CUDA graph (same kernels, same streams): per-step boxes / flips / targets are
         # copied device-to-device into the static buffers the graph reads, then the graph is replayed.  The
         # measurement no longer depends on how fast this host's Python can enqueue ~600 launches per step.
@@ -275,12 +291,10 @@ def run_ours(a):
             opt.step()
             return loss
 
-        _cabi.stats.reset()
         graph = torch.cuda.CUDAGraph()
         with torch.cuda.graph(graph):
             static_loss = body()
         arena.steps -= 1
-        launches_per_step = _cabi.stats.launches
 
         def step(i):  # noqa: F811
             boxes, flips, tgt = params[i]
@@ -310,7 +324,7 @@ def run_ours(a):
     if world > 1:
         dist.all_reduce(ms, op=dist.ReduceOp.MAX)
     ms_total = float(ms.item())
-    launches = launches_per_step * a.steps if graphed else _cabi.stats.launches
+    launches = launches_per_step * a.steps
     final_loss = float(loss.item())
     step = eager_step
     value = a.batch * world * a.steps / (ms_total / 1e3)
@@ -343,7 +357,9 @@ def run_ours(a):
                                     fixed_params=fixed)
         tl = b200.SyntheticImageNet(a.batch, a.steps, a.src, a.image, rank=rank, dtype=dtype, host=True,
                                     fixed_params=fixed)
-        use_graph = b200.GraphedStep(model, crit, opt) if graphed else False
+        use_graph = False
+        if graphed:
+            use_graph = seg_runner if seg_runner is not None else b200.GraphedStep(model, crit, opt)
         b200.train(wl, model, crit, opt, 0, world, sync_every=1, lag=1, graph=use_graph)
         barrier()
         t0 = time.perf_counter()

@@ -21,7 +21,7 @@ from . import _cabi  # noqa: F401
 from ._cabi import B200Error  # noqa: F401
 from .data import DeviceInputStage, SyntheticImageNet, draw_batch_params, rrc_params  # noqa: F401
 from .ddp import DistributedDataParallel, FlatDDP  # noqa: F401
-from .engine import (AverageMeter, GraphedStep, adjust_learning_rate, reduce_tensor, to_python_float, train,  # noqa: F401
+from .engine import (AverageMeter, GraphedStep, SegmentedGraphStep, adjust_learning_rate, reduce_tensor, to_python_float, train,  # noqa: F401
                      validate)
 from .loss import CrossEntropyLoss, accuracy  # noqa: F401
 from .optim import SGD, FlatSGD  # noqa: F401
@@ -31,4 +31,4 @@ from .sampler import DistributedSampler  # noqa: F401
 __all__ = ["B200Error", "B200ResNet", "ParamArena", "build_model", "FlatDDP", "DistributedDataParallel",
            "CrossEntropyLoss", "accuracy", "FlatSGD", "SGD", "DistributedSampler", "DeviceInputStage",
            "SyntheticImageNet", "draw_batch_params", "rrc_params", "AverageMeter", "reduce_tensor",
-           "to_python_float", "adjust_learning_rate", "train", "validate", "GraphedStep"]
+           "to_python_float", "adjust_learning_rate", "train", "validate", "GraphedStep", "SegmentedGraphStep"]

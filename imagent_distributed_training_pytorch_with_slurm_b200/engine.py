@@ -183,6 +183,134 @@ class GraphedStep:
         return self.out3.clone()
 
 
+class SegmentedGraphStep:
+    """The iteration of a multi-process (FlatDDP) run as a CHAIN of CUDA graphs with the NCCL collectives
+    issued eagerly between them.
+
+    Capturing NCCL inside one whole-iteration graph invalidates the capture on this stack, so the capture is
+    cut wherever the backward completes a gradient bucket: graph 0 = forward + loss + backward down to the first
+    bucket boundary, then `all_reduce(bucket 0)` (eager, asynchronous on NCCL's stream), graph 1 = backward down
+    to the next boundary, ... , last graph = the fused SGD step behind the all-reduce waits.  The BatchNorm buffer
+    broadcast (rank 0 wins, as DDP does) is issued after graph 0 and joined before the last graph.  The network
+    is driven directly (its own forward/backward executor, no autograd), so this runner needs the package's own
+    model, criterion and optimizer."""
+
+    WARMUP = 3
+
+    def __init__(self, model, criterion, optimizer):
+        from .ddp import FlatDDP
+        from .optim import FlatSGD
+
+        if not (isinstance(model, FlatDDP) and isinstance(criterion, CrossEntropyLoss) and isinstance(optimizer, FlatSGD)):
+            raise TypeError("SegmentedGraphStep drives FlatDDP(B200ResNet) + CrossEntropyLoss + FlatSGD")
+        self.ddp, self.net, self.criterion, self.optimizer = model, model.module, criterion, optimizer
+        self.eager = GraphedStep(model, criterion, optimizer)
+        self.seen, self.plan, self.x, self.t, self.out3 = 0, None, None, None, None
+        self._cap = torch.cuda.Stream()
+
+    # sink interface used during capture: cut the graph at bucket boundaries
+    def wants(self, offset):
+        return self.ddp.wants(offset)
+
+    def grad_ready(self, offset):
+        d = self.ddp
+        while d._next < len(d.buckets) and d.buckets[d._next][0] >= offset:
+            lo, hi = d.buckets[d._next]
+            self._ctx.__exit__(None, None, None)   # end of this graph ...
+            self.plan.append(self._cur)
+            self.plan.append((lo, hi))             # ... an eager all-reduce of the bucket goes here ...
+            d._next += 1
+            self._cur = torch.cuda.CUDAGraph()     # ... and the next graph begins
+            self._ctx = torch.cuda.graph(self._cur, pool=self._pool, stream=self._cap,
+                                         capture_error_mode="thread_local")
+            self._ctx.__enter__()
+
+    def backward_done(self):
+        self.ddp._next = 0
+
+    def _iteration(self):
+        """forward + loss + backward + optimizer step on the static buffers, driving the network's own
+        executor (no autograd); the current sink decides what happens at bucket boundaries."""
+        from . import _cabi
+
+        net = self.net
+        logits, tape = net._forward_train(net._prep_input(self.x))
+        self.out3, row_lse = _cabi.ce_topk_fwd(logits, self.t)
+        dlogits = _cabi.ce_bwd(logits, self.t, row_lse, None, 1.0)
+        net._backward(tape, dlogits)
+        self.optimizer.step()
+
+    def _manual_eager(self):
+        """One real iteration through ``_iteration`` on the capture stream, un-captured: cuDNN / cuBLAS create
+        per-stream resources lazily and must have seen this stream (and the side stream forked from it) before
+        anything is captured on it."""
+        cur = torch.cuda.current_stream()
+        self._cap.wait_stream(cur)
+        with torch.cuda.stream(self._cap), torch.no_grad():
+            self._iteration()              # sink = the FlatDDP wrapper: eager all-reduces
+            if self.ddp.broadcast_buffers:
+                dist.broadcast(self.net.buffer_arena, 0, group=self.ddp.process_group)
+        cur.wait_stream(self._cap)
+
+    def _capture(self):
+        net = self.net
+        torch.cuda.synchronize()
+        self.plan, self._pool = [], torch.cuda.graph_pool_handle()
+        net.attach_sink(self)
+        try:
+            with torch.no_grad():
+                self._cur = torch.cuda.CUDAGraph()
+                self._ctx = torch.cuda.graph(self._cur, pool=self._pool, stream=self._cap,
+                                             capture_error_mode="thread_local")
+                self._ctx.__enter__()
+                self._iteration()
+                self._ctx.__exit__(None, None, None)
+                self.plan.append(self._cur)
+        finally:
+            net.attach_sink(self.ddp)
+        net.arena.steps -= 1
+        torch.cuda.synchronize()
+
+    def _replay(self):
+        d, works, first = self.ddp, [], True
+        g = self.net.arena.grads
+        for item in self.plan[:-1]:
+            if isinstance(item, tuple):
+                works.append(dist.all_reduce(g[item[0]:item[1]], op=dist.ReduceOp.SUM, group=d.process_group,
+                                             async_op=True))
+            else:
+                item.replay()
+                if first and d.broadcast_buffers:
+                    works.append(dist.broadcast(self.net.buffer_arena, 0, group=d.process_group, async_op=True))
+                first = False
+        for w in works:
+            w.wait()
+        self.plan[-1].replay()
+        self.net.arena.steps += 1
+
+    def __call__(self, x, t):
+        if self.plan is None and self.seen < self.WARMUP:
+            self.seen += 1
+            return self.eager._eager(x, t)
+        if self.x is None:  # the iteration after the eager warm-up: same code path as the capture, un-captured
+            self.x, self.t = torch.empty_like(x), torch.empty_like(t)
+            if hasattr(x, "_b200_s2d_stem"):
+                self.x._b200_s2d_stem = x._b200_s2d_stem
+            self.x.copy_(x)
+            self.t.copy_(t)
+            self.ddp.drain()
+            self._manual_eager()
+            return self.out3.clone()
+        if x.shape != self.x.shape or t.shape != self.t.shape:
+            return self.eager._eager(x, t)
+        self.x.copy_(x)
+        self.t.copy_(t)
+        if self.plan is None:
+            self._capture()
+        self._replay()
+        return self.out3.clone()
+
+
 def _to_device(t):
     return t if t.is_cuda else t.cuda(non_blocking=True)
 
@@ -192,11 +320,12 @@ def train(train_loader, model, criterion, optimizer, epoch, world_size, sync_eve
     losses, top1, top5 = AverageMeter(), AverageMeter(), AverageMeter()
     model.train()
     log, iters = _MetricLog(world_size, (losses, top1, top5), sync_every, lag), 0
-    if graph and world_size > 1:
-        # measured on 2 x B200 (torch 2.11, NCCL 2.28): with the bucket all-reduces / buffer broadcast inside the
-        # step the capture is invalidated (cudaErrorStreamCaptureInvalidated) and the ranks then hang in NCCL
-        raise NotImplementedError("graph=True is implemented for single-process training only")
-    graphed = (graph if isinstance(graph, GraphedStep) else GraphedStep(model, criterion, optimizer)) if graph else None
+    graphed = None
+    if graph:
+        # one whole-iteration graph for a single process; with NCCL inside, the capture is invalidated on this
+        # stack (torch 2.11, NCCL 2.28), so multi-process runs use a chain of graphs cut at the collectives
+        graphed = graph if isinstance(graph, (GraphedStep, SegmentedGraphStep)) else \
+            (SegmentedGraphStep if world_size > 1 else GraphedStep)(model, criterion, optimizer)
     start = end = time.time()
     for i, (input, target) in enumerate(train_loader):
         data_time.update(time.time() - end)

@@ -95,6 +95,7 @@ class _Conv(nn.Module):
                 _, gw, _ = self._cb(gy, x, (False, True, False))
             gy.record_stream(side)
             x.record_stream(side)
+            self.side[1] = True  # work pending on the side stream: the next flush has to join it
             gx = self._cb(gy, x, (True, False, False))[0]
         else:
             gx, gw, _ = self._cb(gy, x, (need_gx, True, False))
@@ -324,7 +325,7 @@ class B200ResNet(nn.Module):
     def _adopt(self, tv):
         """Move the torchvision module's parameters/buffers into flat arenas, keeping key order."""
         self.__dict__["_pending"] = []
-        self.__dict__["_side"] = [None]
+        self.__dict__["_side"] = [None, False]  # [side stream or None, un-joined work pending on it]
         tv_params = dict(tv.named_parameters())
         tv_mods = dict(tv.named_modules())
         names = [n for n, _ in tv.named_parameters()]
@@ -394,8 +395,9 @@ class B200ResNet(nn.Module):
 
     def _flush_grads(self):
         """One K5 launch writes every weight gradient produced since the last flush into the arena."""
-        if self._side[0] is not None:
+        if self._side[0] is not None and self._side[1]:
             torch.cuda.current_stream().wait_stream(self._side[0])
+            self._side[1] = False
         if self._pending:
             _cabi.pack_grads([t for t, _ in self._pending], [o for _, o in self._pending], self.arena.grads)
             self._pending.clear()

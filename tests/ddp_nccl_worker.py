@@ -52,8 +52,25 @@ def main():
     lo, hi = flat.clone(), flat.clone()
     dist.all_reduce(lo, op=dist.ReduceOp.MIN)
     dist.all_reduce(hi, op=dist.ReduceOp.MAX)
+    # the same run again, eager vs the chain of CUDA graphs cut at the collectives (8 iterations: 3 eager
+    # warm-up, 1 capture + replay, 4 replays)
+    graph_res = {}
+    if os.environ.get("B200_TEST_GRAPH", "1") == "1":
+        long_batches = [(x.cuda(), t.cuda()) for x, t in train_cpu.synthetic_batches(rank, 8, 16, 64, 1000, seed=77)]
+        for use_graph in (False, True):
+            torch.manual_seed(5)
+            m = b200.FlatDDP(b200.build_model("resnet18", dtype=torch.bfloat16).cuda(), device_ids=[local],
+                             bucket_cap_mb=8, first_bucket_mb=1)
+            o = b200.FlatSGD(m.parameters(), 0.002, momentum=0.9, weight_decay=1e-4)
+            r = b200.train(long_batches, m, b200.CrossEntropyLoss().cuda(), o, 0, world, sync_every=1, lag=1,
+                           graph=use_graph)
+            sd = m.state_dict()
+            graph_res[str(use_graph)] = {"epoch": list(map(float, r[:3])), "steps": m.module.arena.steps,
+                                         "w": float(sd["module.fc.weight"].double().norm()),
+                                         "rv": float(sd["module.bn1.running_var"].double().norm()),
+                                         "nbt": int(sd["module.bn1.num_batches_tracked"])}
     if rank == 0:
-        print(json.dumps({"ours": list(map(float, o_res[:3])), "stock": list(map(float, r_res[:3])),
+        print(json.dumps({"graph": graph_res, "ours": list(map(float, o_res[:3])), "stock": list(map(float, r_res[:3])),
                           "worst_rel_weight_diff": worst, "worst_key": worst_key, "global_rel_weight_diff": (num / den) ** 0.5, "keys_equal": list(osd) == list(rsd),
                           "replicas_identical": bool(torch.equal(lo, hi)), "buckets": len(ours.buckets)}))
     dist.destroy_process_group()

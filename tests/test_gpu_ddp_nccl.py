@@ -17,7 +17,7 @@ def test_two_gpu_nccl_matches_stock_ddp():
     env = dict(os.environ, PYTHONPATH=ROOT)
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr",
            "127.0.0.1", "--master-port", "29588", os.path.join(ROOT, "tests", "ddp_nccl_worker.py")]
-    r = subprocess.run(cmd, env=env, capture_output=True, text=True, timeout=600)
+    r = subprocess.run(cmd, env=env, capture_output=True, text=True, timeout=240)
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-4000:]
     out = json.loads([l for l in r.stdout.splitlines() if l.startswith("{")][-1])
     assert out["keys_equal"] and out["replicas_identical"] and out["buckets"] >= 3
@@ -26,3 +26,8 @@ def test_two_gpu_nccl_matches_stock_ddp():
     # updated weights after 3 steps (fp32; cuDNN's summation order differs between NHWC and NCHW)
     assert out["global_rel_weight_diff"] < 1e-3, out
     assert out["worst_rel_weight_diff"] < 2e-2, out
+    # eager vs segmented-CUDA-graph execution of the same 8 iterations
+    e, g = out["graph"]["False"], out["graph"]["True"]
+    assert e["steps"] == g["steps"] == 8 and e["nbt"] == g["nbt"] == 8
+    assert e["epoch"][0] == pytest.approx(g["epoch"][0], rel=2e-3) and e["epoch"][1:] == g["epoch"][1:]
+    assert e["w"] == pytest.approx(g["w"], rel=1e-4) and e["rv"] == pytest.approx(g["rv"], rel=1e-3)

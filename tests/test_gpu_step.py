@@ -224,5 +224,3 @@ def test_graphed_training_matches_eager_training():
     assert sa == sb == 10
     assert a[0] == pytest.approx(b[0], rel=1e-3) and a[1] == b[1] and a[2] == b[2]
     assert torch.allclose(ya, yb, rtol=5e-2, atol=5e-2)
-    with pytest.raises(NotImplementedError):
-        b200.train([], torch.nn.Identity(), None, None, 0, 2, graph=True)
