@@ -14,7 +14,8 @@ accuracy                  accuracy                                 (loss.py)
 SGD                       FlatSGD / SGD                            (optim.py)
 DistributedSampler        DistributedSampler                       (sampler.py)
 transforms + DataLoader   DeviceInputStage, SyntheticImageNet      (data.py)
-train / validate / ...    engine.py (same names and signatures)
+train / validate / ...    engine.py (same names and signatures; GraphedStep / SegmentedGraphStep replay
+                          an iteration as CUDA graph(s))
 run / CLI                 imagenet.py
 """
 from . import _cabi  # noqa: F401

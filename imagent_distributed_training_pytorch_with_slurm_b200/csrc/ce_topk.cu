@@ -108,6 +108,7 @@ ce_topk_fwd_kernel(const T *__restrict__ logits, const int64_t *__restrict__ tar
             rows[row] = lse - xt;
             rows[n + row] = (t_ok && ahead < 1) ? 1.f : 0.f;
             rows[2 * n + row] = (t_ok && ahead < 5) ? 1.f : 0.f;
+            __threadfence();  // the row results must be visible device-wide before this block takes its ticket
         }
     }
     // ---- last block to arrive adds the rows up in a fixed order ---------------------------------

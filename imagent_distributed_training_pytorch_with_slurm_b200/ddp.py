@@ -8,7 +8,7 @@ Replaces ``DistributedDataParallel(model, device_ids=[local_rank], output_device
 * every training iteration the BatchNorm buffers of rank 0 overwrite everyone's before the next
   forward (``_sync_buffers``, distributed.py:1590-1591,2214-2257).  Here that is ONE broadcast of the
   contiguous buffer arena, issued right after the forward that updated the statistics so it overlaps
-  the backward, and waited for at the start of the next forward;
+  the backward, and joined at the end of that backward (or at the next forward if there is none);
 * backward: gradients are written by the model straight into the flat arena (no bucket copy-in /
   copy-out); as the backward passes each bucket boundary the slice is all-reduced (SUM) with NCCL on
   its own stream while the rest of the backward keeps the GPU busy.  The 1/world_size pre-division

@@ -5,9 +5,7 @@ ResNet (tape order, residual fan-out, FC / pooling gradients), FlatSGD plumbing,
 train loop and state_dict compatibility - all against stock torchvision + autograd + torch.optim.SGD.
 The CUDA kernels themselves are compared with the oracle in the -m gpu tests.
 """
-import copy
 
-import numpy as np
 import pytest
 import torch
 import torchvision
