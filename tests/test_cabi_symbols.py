@@ -41,3 +41,28 @@ def test_argument_errors_are_reported_not_crashed():
     assert lib.b200_ce_topk_fwd(None, None, None, None, None, 0, 4, 10, 0, None) == 1
     assert lib.b200_bn_fwd_train(None, None, None, None, None, None, None, None, None, None, None, 0, 8, 6, 1e-5, 0.1,
                                  0, 1, None) == 1  # C=6 not a multiple of the bf16 vector width
+
+
+def test_missing_library_fails_loudly(monkeypatch, tmp_path):
+    """No fallback: without the built CUDA library every kernel call raises (nothing routes to the oracle)."""
+    import pytest
+    import torch
+
+    monkeypatch.setattr(cabi, "_lib", None)
+    monkeypatch.setattr(cabi, "LIB_PATH", str(tmp_path / "libb200_imagenet.so"))
+    with pytest.raises(cabi.B200Error, match="no CPU or PyTorch fallback"):
+        cabi.load()
+    with pytest.raises(cabi.B200Error):
+        cabi.tune_set("bn_pdl", 1)
+    # and with the library present, CPU tensors are refused rather than computed some other way
+    monkeypatch.undo()
+    with pytest.raises(cabi.B200Error, match="CUDA tensors"):
+        cabi.sgd_flat(torch.zeros(8), torch.zeros(8), torch.zeros(8), None, 0.1, 0.0, 0.9, 1.0, True)
+
+
+def test_product_package_never_imports_the_oracle():
+    import pathlib
+    pkg = pathlib.Path(cabi.__file__).parent
+    for f in pkg.rglob("*.py"):
+        src = f.read_text()
+        assert "import oracle" not in src and "from oracle" not in src, f
