@@ -174,11 +174,16 @@ def _bn_workspace(x, m, c, dt):
 
 
 
+_retired = []  # outgrown scratch buffers are kept alive: a captured CUDA graph may still point at them
+
+
 def workspace(dev, nbytes, tag, zero=False):
     """Cached per-(device, tag) scratch buffer, grown on demand (PyTorch's allocator owns it)."""
     key = (dev.index, tag)
     buf = _workspaces.get(key)
     if buf is None or buf.numel() < nbytes:
+        if buf is not None:
+            _retired.append(buf)
         n = max(int(nbytes), 256)
         buf = torch.zeros(n, dtype=torch.uint8, device=dev) if zero else torch.empty(n, dtype=torch.uint8, device=dev)
         _workspaces[key] = buf
