@@ -363,6 +363,33 @@ def test_maxpool_matches_oracle(shape, dtype):
         assert np.abs(got - dxo).max() <= np.abs(dxo).max() * 2 ** -8 + 1e-9
 
 
+def test_maxpool_bf16_packed_path_follows_the_scalar_rule_with_nan_inf_and_signed_zero():
+    """The bf16 kernel compares packed pairs; windows holding a NaN are redone by the scalar rule.  Checker: the
+    float32 kernel (scalar rule, pinned against the oracle above) on the same bf16-representable values, and ATen."""
+    g = torch.Generator().manual_seed(11)
+    n, h, w, c = 3, 13, 10, 16
+    x = torch.randn(n, h, w, c, generator=g).relu()
+    x[torch.rand(n, h, w, c, generator=g) < 0.05] = float("nan")
+    x[torch.rand(n, h, w, c, generator=g) < 0.05] = float("-inf")
+    x[torch.rand(n, h, w, c, generator=g) < 0.05] = -0.0
+    x[1, 4:9, 2:7, :] = float("nan")                      # windows made of NaN only: the LAST tap is the argmax
+    x[2, 0:5, 0:5, :] = float("-inf")                     # windows made of -inf only: the FIRST tap in the image
+    xb = x.to(torch.bfloat16)
+    yb, ab = cabi.maxpool_fwd(xb.to(DEV).permute(0, 3, 1, 2))
+    yf, af = cabi.maxpool_fwd(xb.float().to(DEV).permute(0, 3, 1, 2))
+    assert torch.equal(ab, af)
+    assert torch.equal(torch.isnan(yb), torch.isnan(yf))
+    assert torch.equal(torch.nan_to_num(yb.float(), nan=7.0), torch.nan_to_num(yf, nan=7.0))
+    # ATen's contiguous-layout kernel: its channels-last kernel starts an all -inf window at a different index
+    yr, idx = torch.ops.aten.max_pool2d_with_indices(xb.to(DEV).permute(0, 3, 1, 2).contiguous(), [3, 3], [2, 2], [1, 1],
+                                                     [1, 1], False)
+    assert torch.equal(torch.isnan(yb), torch.isnan(yr))
+    oy = torch.arange(yb.shape[2], device=DEV).view(1, 1, -1, 1)
+    ox = torch.arange(yb.shape[3], device=DEV).view(1, 1, 1, -1)
+    pos = (idx // w - (2 * oy - 1)) * 3 + (idx % w - (2 * ox - 1))
+    assert torch.equal(ab.permute(0, 3, 1, 2).long(), pos)
+
+
 def test_maxpool_full_size_against_aten():
     """BASELINE size [256,64,112,112] bf16: the library kernel the reference would have run is the
     checker here (max values and routed gradients must agree exactly / to one bf16 rounding)."""
