@@ -147,11 +147,23 @@ maxpool_bwd_kernel(const T *__restrict__ dy, const uint8_t *__restrict__ arg, T 
 }
 
 // ---- bf16 fast path ---------------------------------------------------------------------------
-// The generic kernels above spend ~5 instructions per tap and channel (unpack, two compares, two selects) and are
-// issue-bound at 2.8 TB/s.  bf16 pairs stay packed here: HSET2 (greater-than mask), HMNMX2 and one LOP3 per tap and
-// PAIR of channels.  Taps outside the image read as -inf, which never wins a strict comparison, and the argmax starts
-// at the first tap inside the image (ATen's initial index), so the tie rule is unchanged.  A window that contains a
-// NaN is redone by the scalar rule ("NaN counts as maximum, the last one wins").
+// The generic kernels above spend ~5 instructions per tap and channel (unpack, two compares, two selects) plus three
+// 64-bit divisions per thread, and are issue-bound at 2.8 TB/s.  Here (a) the index is 32-bit and decoded with
+// multiply-shift division by host-computed constants, (b) bf16 pairs stay packed: HSET2 (greater-than mask), HMNMX2 and
+// one LOP3 per tap and PAIR of channels.  Taps outside the image read as -inf, which never wins a strict comparison,
+// and the argmax starts at the first tap inside the image (ATen's initial index), so the tie rule is unchanged.  A
+// window that contains a NaN is redone by the scalar rule ("NaN counts as maximum, the last one wins").
+struct FastDiv {  // n / d for n < 2^31 (Granlund-Montgomery, round-up variant)
+    unsigned d, mul, shr;
+};
+FastDiv make_fastdiv(unsigned d) {
+    FastDiv f{d, 0u, 0u};
+    while ((1ull << f.shr) < d) ++f.shr;
+    f.mul = (unsigned)((((1ull << f.shr) - d) << 32) / d + 1ull);
+    return f;
+}
+__device__ __forceinline__ unsigned fdiv(unsigned n, const FastDiv &f) { return (__umulhi(n, f.mul) + n) >> f.shr; }
+
 __device__ __forceinline__ __nv_bfloat162 as_bf162(unsigned u) {
     __nv_bfloat162 r;
     *reinterpret_cast<unsigned *>(&r) = u;
@@ -161,26 +173,36 @@ __device__ __forceinline__ unsigned as_u32(__nv_bfloat162 v) { return *reinterpr
 
 __global__ void __launch_bounds__(kThreads)
 maxpool_fwd_bf16_kernel(const __nv_bfloat16 *__restrict__ x, __nv_bfloat16 *__restrict__ y, uint8_t *__restrict__ arg,
-                        int64_t total, int c8, int h, int w, int oh, int ow) {
-    const int64_t gid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+                        unsigned total, FastDiv dc8, FastDiv dow, FastDiv doh, int h, int w) {
+    const unsigned gid = blockIdx.x * kThreads + threadIdx.x;
     if (gid >= total) return;
-    const int cv = (int)(gid % c8);
-    int64_t r = gid / c8;
-    const int ox = (int)(r % ow); r /= ow;
-    const int oy = (int)(r % oh);
-    const int64_t n = r / oh;
-    const int c = c8 * 8;
+    const int c8 = (int)dc8.d;
+    unsigned r = fdiv(gid, dc8);
+    const int cv = (int)(gid - r * dc8.d);
+    unsigned q = fdiv(r, dow);
+    const int ox = (int)(r - q * dow.d);
+    const unsigned n = fdiv(q, doh);
+    const int oy = (int)(q - n * doh.d);
     const int iy0 = oy * 2 - 1, ix0 = ox * 2 - 1;
-    const uint4 *base = reinterpret_cast<const uint4 *>(x + ((n * h + iy0) * w + ix0) * c + cv * 8);
+    const uint4 *base = reinterpret_cast<const uint4 *>(x) + (((int64_t)n * h + iy0) * w + ix0) * c8 + cv;
+    const int rs = w * c8;  // uint4 units; one image row always fits 32 bits here (total < 2^31)
     const unsigned ninf = 0xff80ff80u;
     uint4 v[9];
+    if (iy0 >= 0 && ix0 >= 0 && iy0 + 2 < h && ix0 + 2 < w) {
 #pragma unroll
-    for (int kh = 0; kh < 3; ++kh)
+        for (int kh = 0; kh < 3; ++kh)
 #pragma unroll
-        for (int kw = 0; kw < 3; ++kw) {
-            const bool ok = (unsigned)(iy0 + kh) < (unsigned)h && (unsigned)(ix0 + kw) < (unsigned)w;
-            v[kh * 3 + kw] = ok ? __ldg(base + ((int64_t)kh * w + kw) * c8) : make_uint4(ninf, ninf, ninf, ninf);
-        }
+            for (int kw = 0; kw < 3; ++kw) v[kh * 3 + kw] = __ldg(base + kh * rs + kw * c8);
+    } else {
+#pragma unroll
+        for (int kh = 0; kh < 3; ++kh)
+#pragma unroll
+            for (int kw = 0; kw < 3; ++kw) {
+                const bool ok = (unsigned)(iy0 + kh) < (unsigned)h && (unsigned)(ix0 + kw) < (unsigned)w;
+                v[kh * 3 + kw] = make_uint4(ninf, ninf, ninf, ninf);
+                if (ok) v[kh * 3 + kw] = __ldg(base + kh * rs + kw * c8);
+            }
+    }
     const unsigned first = (unsigned)((iy0 < 0 ? 3 : 0) + (ix0 < 0 ? 1 : 0)) * 0x00010001u;
     __nv_bfloat162 m[4] = {as_bf162(ninf), as_bf162(ninf), as_bf162(ninf), as_bf162(ninf)};
     unsigned pos[4] = {first, first, first, first};
@@ -190,112 +212,118 @@ maxpool_fwd_bf16_kernel(const __nv_bfloat16 *__restrict__ x, __nv_bfloat16 *__re
         const unsigned vv[4] = {v[t].x, v[t].y, v[t].z, v[t].w};
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
-            const __nv_bfloat162 q = as_bf162(vv[j]);
-            const unsigned gt = __hgt2_mask(q, m[j]);
-            m[j] = __hmax2_nan(m[j], q);
+            const __nv_bfloat162 e = as_bf162(vv[j]);
+            const unsigned gt = __hgt2_mask(e, m[j]);
+            m[j] = __hmax2_nan(m[j], e);
             pos[j] = (pos[j] & ~gt) | (tt & gt);
         }
     }
     const unsigned nan = __hneu2_mask(m[0], m[0]) | __hneu2_mask(m[1], m[1]) | __hneu2_mask(m[2], m[2]) |
                          __hneu2_mask(m[3], m[3]);
-    uint4 yo = make_uint4(as_u32(m[0]), as_u32(m[1]), as_u32(m[2]), as_u32(m[3]));
-    uint2 po = make_uint2(__byte_perm(pos[0], pos[1], 0x6420), __byte_perm(pos[2], pos[3], 0x6420));
-    if (nan) {  // rare: redo this window channel by channel with the scalar rule
-        const unsigned short *hv = reinterpret_cast<const unsigned short *>(v);
-        unsigned short best[8];
-        unsigned char bp[8];
-#pragma unroll
-        for (int k = 0; k < 8; ++k) {
-            float b = -INFINITY;
-            unsigned short bb = 0xff80;
-            int p = (int)(first & 0xffu);
-            for (int t = 0; t < 9; ++t) {
-                const int kh = t / 3, kw = t - kh * 3;
-                if ((unsigned)(iy0 + kh) >= (unsigned)h || (unsigned)(ix0 + kw) >= (unsigned)w) continue;
-                const unsigned short raw = hv[t * 8 + k];
-                const float f = __uint_as_float((unsigned)raw << 16);
-                if (f > b || f != f) { b = f; bb = raw; p = t; }
-            }
-            best[k] = bb;
-            bp[k] = (unsigned char)p;
-        }
-        yo = make_uint4(best[0] | (unsigned)best[1] << 16, best[2] | (unsigned)best[3] << 16,
-                        best[4] | (unsigned)best[5] << 16, best[6] | (unsigned)best[7] << 16);
-        po = make_uint2(bp[0] | bp[1] << 8 | bp[2] << 16 | (unsigned)bp[3] << 24,
-                        bp[4] | bp[5] << 8 | bp[6] << 16 | (unsigned)bp[7] << 24);
+    if (nan == 0u) {
+        *reinterpret_cast<uint4 *>(y + (size_t)gid * 8) = make_uint4(as_u32(m[0]), as_u32(m[1]), as_u32(m[2]), as_u32(m[3]));
+        *reinterpret_cast<uint2 *>(arg + (size_t)gid * 8) =
+            make_uint2(__byte_perm(pos[0], pos[1], 0x6420), __byte_perm(pos[2], pos[3], 0x6420));
+        return;
     }
-    *reinterpret_cast<uint4 *>(y + gid * 8) = yo;
-    *reinterpret_cast<uint2 *>(arg + gid * 8) = po;
+    // rare: redo this window channel by channel from memory with the scalar rule
+    const unsigned short *xs = reinterpret_cast<const unsigned short *>(base);
+    unsigned short *ys = reinterpret_cast<unsigned short *>(y) + (size_t)gid * 8;
+#pragma unroll 1
+    for (int k = 0; k < 8; ++k) {
+        float b = -INFINITY;
+        unsigned short bb = 0xff80;
+        int p = (int)(first & 0xffu);
+#pragma unroll 1
+        for (int t = 0; t < 9; ++t) {
+            const int kh = t / 3, kw = t - kh * 3;
+            if ((unsigned)(iy0 + kh) >= (unsigned)h || (unsigned)(ix0 + kw) >= (unsigned)w) continue;
+            const unsigned short raw = xs[(int64_t)(kh * rs + kw * c8) * 8 + k];
+            const float f = __uint_as_float((unsigned)raw << 16);
+            if (f > b || f != f) { b = f; bb = raw; p = t; }
+        }
+        ys[k] = bb;
+        arg[(size_t)gid * 8 + k] = (uint8_t)p;
+    }
 }
 
-// Backward, bf16: gradients and argmax bytes stay packed in registers (24 instead of 64 registers of window state, so
-// twice as many warps are resident to cover the load latency); a byte of `argmax ^ position` is zero where the window
-// routes its gradient to this pixel.
-__global__ void __launch_bounds__(kThreads, 4)
+// Backward, bf16: same patch decomposition as the generic kernel, 32-bit index, window by window: the eight argmax
+// bytes and gradients of a window are unpacked once and compared against the position each pixel of the patch has in
+// that window (one compare + one predicated add per contribution).
+__global__ void __launch_bounds__(kThreads, 3)
 maxpool_bwd_bf16_kernel(const __nv_bfloat16 *__restrict__ dy, const uint8_t *__restrict__ arg,
-                        __nv_bfloat16 *__restrict__ dx, int64_t total, int c8, int h, int w, int oh, int ow) {
-    const int64_t gid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+                        __nv_bfloat16 *__restrict__ dx, unsigned total, FastDiv dc8, FastDiv dpw, FastDiv dph, int h,
+                        int w, int oh, int ow) {
+    const unsigned gid = blockIdx.x * kThreads + threadIdx.x;
     if (gid >= total) return;
-    const int ph = (h + 1) >> 1, pw = (w + 1) >> 1;
-    const int cv = (int)(gid % c8);
-    int64_t r = gid / c8;
-    const int px = (int)(r % pw); r /= pw;
-    const int py = (int)(r % ph);
-    const int64_t n = r / ph;
-    const int c = c8 * 8;
+    const int c8 = (int)dc8.d;
+    unsigned r = fdiv(gid, dc8);
+    const int cv = (int)(gid - r * dc8.d);
+    unsigned q = fdiv(r, dpw);
+    const int px = (int)(r - q * dpw.d);
+    const unsigned n = fdiv(q, dph);
+    const int py = (int)(q - n * dph.d);
     uint4 g[2][2];
     uint2 p[2][2];
+    const unsigned o00 = ((n * (unsigned)oh + py) * ow + px) * c8 + cv;  // < total: fits 32 bits
+    const uint2 *ap = reinterpret_cast<const uint2 *>(arg) + o00;
+    const uint4 *gp = reinterpret_cast<const uint4 *>(dy) + o00;
 #pragma unroll
     for (int a = 0; a < 2; ++a)
 #pragma unroll
         for (int b = 0; b < 2; ++b) {
-            const int oy = py + a, ox = px + b;
-            if (oy < oh && ox < ow) {
-                const int64_t o = (((n * oh + oy) * ow + ox) * c8 + cv) * 8;
-                p[a][b] = __ldg(reinterpret_cast<const uint2 *>(arg + o));
-                g[a][b] = __ldg(reinterpret_cast<const uint4 *>(dy + o));
-            } else {
-                p[a][b] = make_uint2(0xffffffffu, 0xffffffffu);
-                g[a][b] = make_uint4(0u, 0u, 0u, 0u);
+            p[a][b] = make_uint2(0xffffffffu, 0xffffffffu);
+            g[a][b] = make_uint4(0u, 0u, 0u, 0u);
+            if (py + a < oh && px + b < ow) {
+                const int off = (a * ow + b) * c8;
+                p[a][b] = __ldg(ap + off);
+                g[a][b] = __ldg(gp + off);
             }
         }
+    float acc[2][2][8];
 #pragma unroll
-    for (int i = 0; i < 2; ++i) {
-        const int iy = 2 * py + i;
-        if (iy >= h) continue;
+    for (int i = 0; i < 2; ++i)
 #pragma unroll
-        for (int j = 0; j < 2; ++j) {
-            const int ix = 2 * px + j;
-            if (ix >= w) continue;
-            float acc[8];
+        for (int j = 0; j < 2; ++j)
 #pragma unroll
-            for (int k = 0; k < 8; ++k) acc[k] = 0.f;
+            for (int k = 0; k < 8; ++k) acc[i][j][k] = 0.f;
 #pragma unroll
-            for (int a = 0; a < 2; ++a) {
-                const int kh = i + 1 - 2 * a;
-                if (kh < 0 || kh > 2) continue;
+    for (int a = 0; a < 2; ++a)
 #pragma unroll
-                for (int b = 0; b < 2; ++b) {
-                    const int kw = j + 1 - 2 * b;
-                    if (kw < 0 || kw > 2) continue;
-                    const unsigned me4 = (unsigned)(kh * 3 + kw) * 0x01010101u;
-                    const unsigned d0 = p[a][b].x ^ me4, d1 = p[a][b].y ^ me4;
-                    const unsigned gw[4] = {g[a][b].x, g[a][b].y, g[a][b].z, g[a][b].w};
+        for (int b = 0; b < 2; ++b) {
+            const unsigned gw[4] = {g[a][b].x, g[a][b].y, g[a][b].z, g[a][b].w};
 #pragma unroll
-                    for (int k = 0; k < 8; ++k) {
-                        const unsigned d = (k < 4 ? d0 : d1) & (0xffu << ((k & 3) * 8));
-                        const unsigned word = gw[k >> 1];
-                        const float f = __uint_as_float((k & 1) ? (word & 0xffff0000u) : (word << 16));
-                        if (d == 0u) acc[k] += f;
+            for (int k = 0; k < 8; ++k) {
+                const unsigned pk = __byte_perm(k < 4 ? p[a][b].x : p[a][b].y, 0u, 0x4440u | (k & 3));
+                const float f = __uint_as_float((k & 1) ? (gw[k >> 1] & 0xffff0000u) : (gw[k >> 1] << 16));
+#pragma unroll
+                for (int i = 0; i < 2; ++i) {
+                    const int kh = i + 1 - 2 * a;
+                    if (kh < 0) continue;
+#pragma unroll
+                    for (int j = 0; j < 2; ++j) {
+                        const int kw = j + 1 - 2 * b;
+                        if (kw < 0) continue;
+                        asm("{\n\t.reg .pred q;\n\tsetp.eq.u32 q, %1, %2;\n\t@q add.f32 %0, %0, %3;\n\t}"
+                            : "+f"(acc[i][j][k])
+                            : "r"(pk), "r"((unsigned)(kh * 3 + kw)), "f"(f));  // compare + predicated add
                     }
                 }
             }
+        }
+    uint4 *xp = reinterpret_cast<uint4 *>(dx) + (((size_t)n * h + 2 * py) * w + 2 * px) * c8 + cv;
+#pragma unroll
+    for (int i = 0; i < 2; ++i) {
+        if (2 * py + i >= h) continue;
+#pragma unroll
+        for (int j = 0; j < 2; ++j) {
+            if (2 * px + j >= w) continue;
             uint4 o;
-            o.x = as_u32(__floats2bfloat162_rn(acc[0], acc[1]));
-            o.y = as_u32(__floats2bfloat162_rn(acc[2], acc[3]));
-            o.z = as_u32(__floats2bfloat162_rn(acc[4], acc[5]));
-            o.w = as_u32(__floats2bfloat162_rn(acc[6], acc[7]));
-            *reinterpret_cast<uint4 *>(dx + ((n * h + iy) * w + ix) * c + cv * 8) = o;
+            o.x = as_u32(__floats2bfloat162_rn(acc[i][j][0], acc[i][j][1]));
+            o.y = as_u32(__floats2bfloat162_rn(acc[i][j][2], acc[i][j][3]));
+            o.z = as_u32(__floats2bfloat162_rn(acc[i][j][4], acc[i][j][5]));
+            o.w = as_u32(__floats2bfloat162_rn(acc[i][j][6], acc[i][j][7]));
+            xp[(i * w + j) * c8] = o;
         }
     }
 }
@@ -311,10 +339,14 @@ extern "C" int b200_maxpool3x3s2_fwd(const void *x, void *y, uint8_t *argmax, in
     const int64_t total = n * oh * ow * (c / 8);
     const unsigned blocks = (unsigned)((total + kThreads - 1) / kThreads);
     cudaStream_t st = static_cast<cudaStream_t>(stream);
-    if (dtype == B200_BF16)
+    if (dtype == B200_BF16 && total < (1ll << 31))
         maxpool_fwd_bf16_kernel<<<blocks, kThreads, 0, st>>>(static_cast<const __nv_bfloat16 *>(x),
-                                                            static_cast<__nv_bfloat16 *>(y), argmax, total, c / 8, h, w,
-                                                            oh, ow);
+                                                            static_cast<__nv_bfloat16 *>(y), argmax, (unsigned)total,
+                                                            make_fastdiv(c / 8), make_fastdiv(ow), make_fastdiv(oh), h, w);
+    else if (dtype == B200_BF16)
+        maxpool_fwd_kernel<__nv_bfloat16><<<blocks, kThreads, 0, st>>>(static_cast<const __nv_bfloat16 *>(x),
+                                                                      static_cast<__nv_bfloat16 *>(y), argmax, total,
+                                                                      c / 8, h, w, oh, ow);
     else
         maxpool_fwd_kernel<float><<<blocks, kThreads, 0, st>>>(static_cast<const float *>(x), static_cast<float *>(y),
                                                               argmax, total, c / 8, h, w, oh, ow);
@@ -331,9 +363,15 @@ extern "C" int b200_maxpool3x3s2_bwd(const void *dy, const uint8_t *argmax, void
     const int64_t total = n * ((h + 1) / 2) * ((w + 1) / 2) * (c / 8);
     const unsigned blocks = (unsigned)((total + kThreads - 1) / kThreads);
     cudaStream_t st = static_cast<cudaStream_t>(stream);
-    if (dtype == B200_BF16)
+    if (dtype == B200_BF16 && total < (1ll << 31))
         maxpool_bwd_bf16_kernel<<<blocks, kThreads, 0, st>>>(static_cast<const __nv_bfloat16 *>(dy), argmax,
-                                                            static_cast<__nv_bfloat16 *>(dx), total, c / 8, h, w, oh, ow);
+                                                            static_cast<__nv_bfloat16 *>(dx), (unsigned)total,
+                                                            make_fastdiv(c / 8), make_fastdiv((w + 1) / 2),
+                                                            make_fastdiv((h + 1) / 2), h, w, oh, ow);
+    else if (dtype == B200_BF16)
+        maxpool_bwd_kernel<__nv_bfloat16><<<blocks, kThreads, 0, st>>>(static_cast<const __nv_bfloat16 *>(dy), argmax,
+                                                                      static_cast<__nv_bfloat16 *>(dx), total, c / 8, h,
+                                                                      w, oh, ow);
     else
         maxpool_bwd_kernel<float><<<blocks, kThreads, 0, st>>>(static_cast<const float *>(dy), argmax,
                                                               static_cast<float *>(dx), total, c / 8, h, w, oh, ow);
