@@ -366,6 +366,38 @@ def run_ours(a):
     fam = _cabi.stats.summary()
     model.module.use_wgrad_stream(overlapped)
 
+    # ---- the gradient exchange alone (N > 1): the bucket all-reduces of one iteration, back to back, on a
+    # scratch copy of the gradient arena; bus bandwidth = 2(W-1)/W x bytes / time (the NCCL-tests definition) ----
+    allreduce = None
+    if world > 1:
+        try:
+            scratch = torch.zeros_like(model.module.arena.grads)
+            reps = 10
+
+            def exchange():
+                for lo, hi in model.buckets:
+                    dist.all_reduce(scratch[lo:hi], op=dist.ReduceOp.SUM)
+
+            for _ in range(3):
+                exchange()
+            barrier()
+            c0, c1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            c0.record()
+            for _ in range(reps):
+                exchange()
+            c1.record()
+            barrier()
+            t = torch.tensor([c0.elapsed_time(c1) / reps], device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            nbytes = scratch.numel() * scratch.element_size()
+            alg = nbytes / 1e9 / (float(t.item()) / 1e3)
+            allreduce = {"bytes": nbytes, "buckets": len(model.buckets), "ms": float(t.item()), "algbw_GBps": alg,
+                         "busbw_GBps": alg * 2 * (world - 1) / world, "nvlink_peak_GBps_per_direction": 900.0,
+                         "note": "timed alone, not overlapped with the backward; in the step it hides behind it"}
+            del scratch
+        except Exception as e:  # noqa: BLE001
+            notes.append(f"allreduce timing failed: {type(e).__name__}: {str(e)[:200]}")
+
     # ---- end to end through the public API with HOST buffers ------------------------------------
     e2e = None
     if not a.no_e2e:
@@ -433,7 +465,7 @@ def run_ours(a):
                        "l2": "not flushed: one step streams >10 GB of activations, far larger than the 126 MB L2",
                        "wgrad_side_stream": overlapped, "cuda_graph_replay": graphed},
             "e2e": e2e, "gpu_launches": launches, "clocks": clocks, "roofline": roof, "cpu_baseline": cpu,
-            "kernels": kernels, "final_loss": final_loss, "host_enqueue_ms_per_step": host_ms, "notes": notes,
+            "kernels": kernels, "allreduce": allreduce, "final_loss": final_loss, "host_enqueue_ms_per_step": host_ms, "notes": notes,
         }
         print(json.dumps(out))
     if world > 1:

@@ -18,6 +18,8 @@
 // because the resized pixel is an 8-bit value.
 #include "common.cuh"
 
+int g_input_s2d_fast = 1;  // b200_tune_set("input_s2d_fast"): 0 sends the stem layout through the generic kernel
+
 namespace {
 
 constexpr int kThreads = 256;
@@ -241,6 +243,206 @@ input_resample_kernel(const uint8_t *__restrict__ images, const int32_t *__restr
     }
 }
 
+// ---- space-to-depth fast path -------------------------------------------------------------------
+// The generic kernel above spends ~270 instructions per output pixel (byte loads from global memory in the horizontal
+// pass, byte-wise shared-memory traffic and per-pixel index arithmetic in the vertical pass) and is issue-bound.  The
+// stem layout - the one the model consumes - gets its own kernel built on 32-bit RGBx pixels in shared memory:
+//   1. the needed rows of the crop box are staged as RGBx words (word loads + funnel shift, 4 pixels per thread step);
+//   2. horizontal pass: one 32-bit shared load per tap, one 32-bit store per intermediate pixel;
+//   3. vertical pass: a thread owns one 16-channel CELL (2x2 pixels): one 64-bit shared load per tap and row, 12
+//      look-ups, and the finished cell leaves with 16-byte stores straight to global memory (a warp writes 1 KB
+//      contiguous) - border cells and the 4 spare channels are written as zeros, so there is no staged tile.
+// clip8 needs no clamp for the bilinear filter: weights are >= 0 and sum to 2^22 + (<= taps/2), so
+// 2^21 + 255 * sum < 256 * 2^22; `min` is kept as a guard.
+constexpr int kS2dPadWords = 4;
+
+template <typename OutT>
+__device__ __forceinline__ void store_cell(OutT *dst, const float (&f)[12]);
+template <>
+__device__ __forceinline__ void store_cell<float>(float *dst, const float (&f)[12]) {
+    float4 *d = reinterpret_cast<float4 *>(dst);
+    d[0] = make_float4(f[0], f[1], f[2], f[3]);
+    d[1] = make_float4(f[4], f[5], f[6], f[7]);
+    d[2] = make_float4(f[8], f[9], f[10], f[11]);
+    d[3] = make_float4(0.f, 0.f, 0.f, 0.f);
+}
+template <>
+__device__ __forceinline__ void store_cell<__nv_bfloat16>(__nv_bfloat16 *dst, const float (&f)[12]) {
+    unsigned w[6];
+#pragma unroll
+    for (int i = 0; i < 6; ++i) {
+        const __nv_bfloat162 h = __floats2bfloat162_rn(f[2 * i], f[2 * i + 1]);
+        w[i] = *reinterpret_cast<const unsigned *>(&h);
+    }
+    uint4 *d = reinterpret_cast<uint4 *>(dst);
+    d[0] = make_uint4(w[0], w[1], w[2], w[3]);
+    d[1] = make_uint4(w[4], w[5], 0u, 0u);
+}
+
+template <typename OutT>
+__global__ void __launch_bounds__(kThreads)
+input_s2d_kernel(const uint8_t *__restrict__ images, int64_t image_bytes, const int32_t *__restrict__ boxes,
+                 const uint8_t *__restrict__ flips, OutT *__restrict__ out, const int32_t *__restrict__ ws, int src_h,
+                 int src_w, int out_h, int out_w, int KX, int KY, int max_src_rows, Norm nrm, int src_stride,
+                 int inter_stride) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    float *lut = reinterpret_cast<float *>(smem_raw);                        // [3][256]
+    uint32_t *src = reinterpret_cast<uint32_t *>(smem_raw + 3 * 256 * sizeof(float));  // [max_src_rows][src_stride]
+    uint32_t *inter = src + (size_t)max_src_rows * src_stride;              // [max_src_rows][inter_stride]
+
+    const int64_t s = blockIdx.y;
+    const int ya = (int)blockIdx.x * kTileRows - 3;   // first output row of the tile (may be < 0)
+    const int y0 = ya < 0 ? 0 : ya;
+    const int y1 = (ya + kTileRows < out_h) ? ya + kTileRows : out_h;
+    const int sy = (out_h + 6) >> 1, sx = (out_w + 6) >> 1;
+    for (int i = threadIdx.x; i < 3 * 256; i += kThreads) {
+        const int ch = i >> 8, v = i & 255;
+        lut[i] = __fdiv_rn(__fsub_rn(__fdiv_rn((float)v, 255.0f), nrm.mean[ch]), nrm.std[ch]);
+    }
+    const int64_t per_sample = (int64_t)out_w * (2 + KX) + (int64_t)out_h * (2 + KY);
+    const int32_t *bx = ws + s * per_sample;
+    const int32_t *cx = bx + 2 * out_w;
+    const int32_t *by = bx + (int64_t)out_w * (2 + KX);
+    const int32_t *cy = by + 2 * out_h;
+    const int top = boxes[s * 4 + 0], left = boxes[s * 4 + 1], bw = boxes[s * 4 + 3];
+    const bool flip = flips && flips[s] != 0;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    int ylo = 0;
+    bool rows_ok = y1 > y0;
+    if (rows_ok) {
+        ylo = by[2 * y0];
+        const int nrows = by[2 * (y1 - 1)] + by[2 * (y1 - 1) + 1] - ylo;
+        rows_ok = nrows <= max_src_rows && bw <= src_stride - kS2dPadWords;   // else: contract violation
+        if (rows_ok) {
+            // 1. stage the rows: 4 pixels = 12 bytes = (up to) 4 aligned words per step
+            const int ngroups = (bw + 3) >> 2;
+            for (int rr = warp; rr < nrows; rr += kThreads / 32) {
+                const int64_t off = (((int64_t)s * src_h + top + ylo + rr) * src_w + left) * 3;
+                const uintptr_t addr = reinterpret_cast<uintptr_t>(images) + (uintptr_t)off;
+                const unsigned sh = (unsigned)(addr & 3) * 8u;
+                const uint8_t *a0 = reinterpret_cast<const uint8_t *>(addr & ~(uintptr_t)3);
+                const int64_t o0 = off - (int64_t)(addr & 3);   // offset of a0 relative to `images` (may be -3..0)
+                uint4 *drow = reinterpret_cast<uint4 *>(src + (size_t)rr * src_stride);
+                const bool safe = o0 >= 0 && o0 + 12 * (int64_t)ngroups + 4 <= image_bytes;
+                for (int j = lane; j < ngroups; j += 32) {
+                    unsigned w[4];
+                    if (safe) {
+#pragma unroll
+                        for (int q = 0; q < 4; ++q) w[q] = __ldg(reinterpret_cast<const unsigned *>(a0 + 12 * j + 4 * q));
+                    } else {  // first / last bytes of the whole batch: assemble from the bytes that exist
+#pragma unroll
+                        for (int q = 0; q < 4; ++q) {
+                            const int64_t o = o0 + 12 * (int64_t)j + 4 * q;
+                            w[q] = 0u;
+#pragma unroll
+                            for (int b = 0; b < 4; ++b)
+                                if (o + b >= 0 && o + b < image_bytes) w[q] |= (unsigned)images[o + b] << (8 * b);
+                        }
+                    }
+                    const unsigned b0 = __funnelshift_r(w[0], w[1], sh), b1 = __funnelshift_r(w[1], w[2], sh),
+                                   b2 = __funnelshift_r(w[2], w[3], sh);
+                    drow[j] = make_uint4(b0, __byte_perm(b0, b1, 0x0543), __byte_perm(b1, b2, 0x0432), b2 >> 8);
+                }
+            }
+            __syncthreads();
+            // 2. horizontal pass: a thread owns an output column (taps in registers) and walks down the rows
+            for (int xx = threadIdx.x; xx < out_w; xx += kThreads) {
+                const int xmin = bx[2 * xx], cnt = bx[2 * xx + 1];
+                const int32_t *k = cx + (int64_t)xx * KX;
+                const uint32_t *px = src + xmin;
+                uint32_t *o = inter + xx + 1;
+                if (cnt <= 4) {
+                    int kk[4];
+#pragma unroll
+                    for (int t = 0; t < 4; ++t) kk[t] = (t < cnt) ? k[t] : 0;   // zero taps read the row padding
+                    for (int rr = 0; rr < nrows; ++rr, px += src_stride, o += inter_stride) {
+                        int a0 = 1 << (kPrecisionBits - 1), a1 = a0, a2 = a0;
+#pragma unroll
+                        for (int t = 0; t < 4; ++t) {
+                            if (t < 2 || t < cnt) {
+                                const unsigned w = px[t];
+                                a0 += (int)(w & 0xffu) * kk[t];
+                                a1 += (int)((w >> 8) & 0xffu) * kk[t];
+                                a2 += (int)((w >> 16) & 0xffu) * kk[t];
+                            }
+                        }
+                        *o = (unsigned)min(a0 >> kPrecisionBits, 255) | ((unsigned)min(a1 >> kPrecisionBits, 255) << 8) |
+                             ((unsigned)min(a2 >> kPrecisionBits, 255) << 16);
+                    }
+                } else {  // stronger down-scaling: taps stay in memory
+                    for (int rr = 0; rr < nrows; ++rr, px += src_stride, o += inter_stride) {
+                        int a0 = 1 << (kPrecisionBits - 1), a1 = a0, a2 = a0;
+                        for (int t = 0; t < cnt; ++t) {
+                            const int kt = k[t];
+                            const unsigned w = px[t];
+                            a0 += (int)(w & 0xffu) * kt;
+                            a1 += (int)((w >> 8) & 0xffu) * kt;
+                            a2 += (int)((w >> 16) & 0xffu) * kt;
+                        }
+                        *o = (unsigned)min(a0 >> kPrecisionBits, 255) | ((unsigned)min(a1 >> kPrecisionBits, 255) << 8) |
+                             ((unsigned)min(a2 >> kPrecisionBits, 255) << 16);
+                    }
+                }
+            }
+            __syncthreads();
+        }
+    } else {
+        __syncthreads();   // the look-up table
+    }
+    // 3. vertical pass, one cell per thread step: 64 threads per cell row
+    const int cyl = threadIdx.x >> 6;
+    const int cyy = (int)blockIdx.x * 4 + cyl;
+    if (cyy >= sy) return;
+    const int yy0 = 2 * cyy - 3;
+    OutT *orow = out + (((int64_t)s * sy + cyy) * sx << 4);
+    int ymin[2], ycnt[2];
+#pragma unroll
+    for (int r = 0; r < 2; ++r) {
+        const int yy = yy0 + r;
+        const bool ok = rows_ok && yy >= 0 && yy < out_h;
+        ymin[r] = ok ? by[2 * yy] - ylo : 0;
+        ycnt[r] = ok ? by[2 * yy + 1] : 0;
+    }
+    for (int cxx = threadIdx.x & 63; cxx < sx; cxx += 64) {
+        const int xd0 = 2 * cxx - 3;
+        float f[12];
+#pragma unroll
+        for (int i = 0; i < 12; ++i) f[i] = 0.f;
+        const bool v0 = xd0 >= 0 && xd0 < out_w, v1 = xd0 + 1 >= 0 && xd0 + 1 < out_w;
+        if (v0 || v1) {
+            // words x+1 of the two source columns are an aligned pair: (2cx-2, 2cx-1), mirrored when flipping
+            const int pair = flip ? out_w + 2 - 2 * cxx : 2 * cxx - 2;
+#pragma unroll
+            for (int r = 0; r < 2; ++r) {
+                if (ycnt[r] == 0) continue;
+                const int32_t *k = cy + (int64_t)(yy0 + r) * KY;
+                const uint32_t *p = inter + (size_t)ymin[r] * inter_stride + pair;
+                int a[6];
+#pragma unroll
+                for (int i = 0; i < 6; ++i) a[i] = 1 << (kPrecisionBits - 1);
+                for (int t = 0; t < ycnt[r]; ++t, p += inter_stride) {
+                    const int kt = k[t];
+                    const uint2 w = *reinterpret_cast<const uint2 *>(p);
+                    a[0] += (int)(w.x & 0xffu) * kt;
+                    a[1] += (int)((w.x >> 8) & 0xffu) * kt;
+                    a[2] += (int)((w.x >> 16) & 0xffu) * kt;
+                    a[3] += (int)(w.y & 0xffu) * kt;
+                    a[4] += (int)((w.y >> 8) & 0xffu) * kt;
+                    a[5] += (int)((w.y >> 16) & 0xffu) * kt;
+                }
+                // a[0..2] = lower source column, a[3..5] = upper; destination order swaps them when flipping
+#pragma unroll
+                for (int ch = 0; ch < 3; ++ch) {
+                    const int e0 = flip ? a[3 + ch] : a[ch], e1 = flip ? a[ch] : a[3 + ch];
+                    if (v0) f[r * 6 + ch] = lut[ch * 256 + min(e0 >> kPrecisionBits, 255)];
+                    if (v1) f[r * 6 + 3 + ch] = lut[ch * 256 + min(e1 >> kPrecisionBits, 255)];
+                }
+            }
+        }
+        store_cell<OutT>(orow + ((int64_t)cxx << 4), f);
+    }
+}
+
 int max_src_rows_for(int src_h, int out_h) {
     const double s = (double)src_h / (double)out_h;
     const double sup = s < 1.0 ? 1.0 : s;
@@ -278,6 +480,33 @@ extern "C" int b200_input_crop_resize_flip_norm(const uint8_t *images, const int
     B200_CHECK_LAUNCH();
     const int max_rows = max_src_rows_for(src_h, out_h);
     const size_t esz = out_dtype == B200_F32 ? 4 : 2;
+    if (out_layout == B200_LAYOUT_S2D_STEM && g_input_s2d_fast) {
+        const int src_stride = (src_w + kS2dPadWords + 3) / 4 * 4, inter_stride = out_w + 2;
+        const size_t smem2 = 3 * 256 * sizeof(float) + (size_t)max_rows * (src_stride + inter_stride) * sizeof(uint32_t);
+        if (smem2 <= 96 * 1024) {   // larger boxes / stronger down-scaling use the generic kernel below
+            Norm nrm2;
+            for (int i = 0; i < 3; ++i) { nrm2.mean[i] = mean3[i]; nrm2.std[i] = std3[i]; }
+            const dim3 grid2((out_h + 6 + kTileRows - 1) / kTileRows, (unsigned)n);
+            const int64_t image_bytes = n * (int64_t)src_h * src_w * 3;
+            cudaError_t e = cudaSuccess;
+            if (out_dtype == B200_F32) {
+                auto kern = input_s2d_kernel<float>;
+                if (smem2 > 48 * 1024) e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2);
+                if (e != cudaSuccess) return (int)e;
+                kern<<<grid2, kThreads, smem2, st>>>(images, image_bytes, boxes, flips, static_cast<float *>(out), ws, src_h,
+                                                     src_w, out_h, out_w, KX, KY, max_rows, nrm2, src_stride, inter_stride);
+            } else {
+                auto kern = input_s2d_kernel<__nv_bfloat16>;
+                if (smem2 > 48 * 1024) e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2);
+                if (e != cudaSuccess) return (int)e;
+                kern<<<grid2, kThreads, smem2, st>>>(images, image_bytes, boxes, flips, static_cast<__nv_bfloat16 *>(out), ws,
+                                                     src_h, src_w, out_h, out_w, KX, KY, max_rows, nrm2, src_stride,
+                                                     inter_stride);
+            }
+            B200_CHECK_LAUNCH();
+            return 0;
+        }
+    }
     const int inter_bytes = (int)(((size_t)max_rows * out_w * 3 + 15) / 16 * 16);
     size_t tile_bytes = 0;
     if (out_layout == B200_LAYOUT_NHWC) tile_bytes = (size_t)kTileRows * out_w * 3 * esz;

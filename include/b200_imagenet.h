@@ -49,6 +49,8 @@ const char *b200_error_string(int code);
  *   "bn_pdl"           1 = the finalize/apply kernels of the bulk-async path are launched with programmatic
  *                      dependent launch (they start while their predecessor drains), default 1
  *   "bn_pipe_stages"   shared-memory ring depth of the bulk-async kernels, 2..8 (default 0 = automatic)
+ *   "input_s2d_fast"   1 (default): B200_LAYOUT_S2D_STEM output is produced by the cell-per-thread kernel;
+ *                      0: by the generic kernel (same bits, slower; kept as the in-library cross-check)
  * Returns cudaErrorInvalidValue for an unknown key or value. */
 int b200_tune_set(const char *key, int value);
 

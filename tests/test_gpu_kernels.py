@@ -160,8 +160,12 @@ def _bn_check(m, c, act, dtype, vec, seed, eps=1e-5, momentum=0.1):
     safe = (np.abs(pre) > 1e-4) if act != cabi.ACT_NONE else np.ones_like(pre, dtype=bool)
     assert (~safe).mean() < 1e-3
     scale = np.abs(dgo).max() + np.abs(dbo).max()
-    assert np.allclose(db.cpu().numpy(), dbo, rtol=1e-4, atol=1e-4 * scale + 1e-3)
-    assert np.allclose(dg.cpu().numpy(), dgo, rtol=1e-4, atol=1e-4 * scale + 1e-3)
+    # an excluded element that took the other side of the ReLU moves its channel's sums by its own gradient
+    xhat = (xs.astype(np.float64) - mean) * invstd
+    slack_b = (np.abs(dys) * ~safe).sum(0)
+    slack_g = (np.abs(dys * xhat) * ~safe).sum(0)
+    assert np.all(np.abs(db.cpu().numpy() - dbo) <= 1e-4 * np.abs(dbo) + 1e-4 * scale + 1e-3 + slack_b)
+    assert np.all(np.abs(dg.cpu().numpy() - dgo) <= 1e-4 * np.abs(dgo) + 1e-4 * scale + 1e-3 + slack_g)
     dxk = dx.float().cpu().numpy()
     if bf:
         assert (np.abs(dxk - dxo)[safe]).max() <= np.abs(dxo).max() * 2 ** -7
@@ -404,21 +408,45 @@ def test_maxpool_full_size_against_aten():
     assert (dx.float() - dxr.float()).abs().max().item() <= dxr.float().abs().max().item() * 2 ** -7
 
 
-def test_input_stage_space_to_depth_layout_is_a_reindexing():
-    rng = np.random.default_rng(3)
-    n, sh, sw, oh, ow = 4, 90, 70, 64, 48
+@pytest.mark.parametrize("sh,sw,oh,ow", [(90, 70, 64, 48), (256, 256, 224, 224), (500, 375, 448, 448),
+                                         (100, 120, 224, 224), (33, 57, 8, 10), (224, 224, 224, 224),
+                                         (300, 480, 96, 96)])
+def test_input_stage_space_to_depth_layout_is_a_reindexing(sh, sw, oh, ow):
+    """The stem layout has its own kernel (RGBx words in shared memory, one cell per thread); it must be the oracle's
+    image re-indexed, bit for bit, and identical to the generic kernel's output for that layout."""
+    rng = np.random.default_rng(3 + sh)
+    n = 6
     images = rng.integers(0, 256, (n, sh, sw, 3), dtype=np.uint8)
     from imagent_distributed_training_pytorch_with_slurm_b200.data import draw_batch_params
     boxes, flips = draw_batch_params(n, sh, sw, torch.Generator().manual_seed(1))
+    boxes, flips = boxes.clone(), flips.clone()
+    boxes[0] = torch.tensor([0, 0, sh, sw])                  # whole image (first bytes of the batch)
+    boxes[1] = torch.tensor([sh - 1, sw - 1, 1, 1])          # single pixel, pure up-scaling
+    boxes[2] = torch.tensor([0, sw // 2, sh, 1])             # one column
+    boxes[n - 1] = torch.tensor([sh // 2, sw // 3, sh - sh // 2, sw - sw // 3])   # ends at the last byte of the batch
+    flips[0], flips[1], flips[n - 1] = 0, 1, 1
     mean, std = (0.485, 0.456, 0.406), (0.229, 0.224, 0.225)
     ref = oin.input_stage_oracle(images, boxes.numpy(), flips.numpy().astype(bool), oh, ow, mean, std)
     want = oin.space_to_depth_stem_oracle(ref)
-    for dtype in (torch.float32, torch.bfloat16):
-        out = cabi.input_stage(torch.from_numpy(images).to(DEV), boxes.to(DEV), flips.to(DEV), oh, ow, mean, std, dtype,
-                               cabi.LAYOUT_S2D_STEM)
-        assert out.shape == (n, 16, (oh + 6) // 2, (ow + 6) // 2) and out._b200_s2d_stem == (oh, ow)
-        got = out.float().cpu().permute(0, 2, 3, 1).numpy()
-        assert np.array_equal(got, want if dtype == torch.float32 else _bf16_round(want))
+    # the images live at an odd byte offset inside a larger allocation: exercises the unaligned word loads
+    backing = torch.zeros(images.size + 7, dtype=torch.uint8, device=DEV)
+    for shift in (0, 3):
+        dev_images = backing[shift:shift + images.size].view(n, sh, sw, 3)
+        dev_images.copy_(torch.from_numpy(images))
+        for dtype in (torch.float32, torch.bfloat16):
+            outs = []
+            for fast in (1, 0):
+                cabi.tune_set("input_s2d_fast", fast)
+                try:
+                    out = cabi.input_stage(dev_images, boxes.to(DEV), flips.to(DEV), oh, ow, mean, std, dtype,
+                                           cabi.LAYOUT_S2D_STEM)
+                finally:
+                    cabi.tune_set("input_s2d_fast", 1)
+                assert out.shape == (n, 16, (oh + 6) // 2, (ow + 6) // 2) and out._b200_s2d_stem == (oh, ow)
+                outs.append(out)
+            got = outs[0].float().cpu().permute(0, 2, 3, 1).numpy()
+            assert np.array_equal(got, want if dtype == torch.float32 else _bf16_round(want))
+            assert torch.equal(outs[0], outs[1])
 
 
 # ------------------------------------------------------------------------------------------------ K5
