@@ -39,11 +39,18 @@ __device__ __forceinline__ double tri_weight(double x) {
 }
 
 // tables per sample: bounds_x[out_w][2], coef_x[out_w][KX], bounds_y[out_h][2], coef_y[out_h][KY]
+struct Norm { float mean[3]; float std[3]; };
+
 __global__ void __launch_bounds__(kThreads)
 input_coeff_kernel(const int32_t *__restrict__ boxes, int64_t n, int out_h, int out_w, int KX, int KY,
-                   int32_t *__restrict__ ws) {
+                   int32_t *__restrict__ ws, float *__restrict__ lut, Norm nrm) {
     const int per_row = out_w + out_h;
     const int64_t gid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (lut && gid < 3 * 256) {
+        // ToTensor: float32(v) / 255 ; Normalize: (x - mean) / std, all IEEE float32
+        const int ch = (int)gid >> 8, v = (int)gid & 255;
+        lut[gid] = __fdiv_rn(__fsub_rn(__fdiv_rn((float)v, 255.0f), nrm.mean[ch]), nrm.std[ch]);
+    }
     if (gid >= n * per_row) return;
     const int64_t s = gid / per_row;
     const int idx = (int)(gid - s * per_row);
@@ -96,8 +103,6 @@ template <>
 __device__ __forceinline__ float cast_out<float>(float v) { return v; }
 template <>
 __device__ __forceinline__ __nv_bfloat16 cast_out<__nv_bfloat16>(float v) { return __float2bfloat16_rn(v); }
-
-struct Norm { float mean[3]; float std[3]; };
 
 // One CTA = one tile of 8 output rows of one sample.  Output rows of a tile are assembled in shared
 // memory in their final memory layout and leave with 16-byte vector stores (NHWC: 8 contiguous rows;
@@ -253,7 +258,7 @@ input_resample_kernel(const uint8_t *__restrict__ images, const int32_t *__restr
 //      look-ups, and the finished cell leaves with 16-byte stores straight to global memory (a warp writes 1 KB
 //      contiguous) - border cells and the 4 spare channels are written as zeros, so there is no staged tile.
 // clip8 needs no clamp for the bilinear filter: weights are >= 0 and sum to 2^22 + (<= taps/2), so
-// 2^21 + 255 * sum < 256 * 2^22; `min` is kept as a guard.
+// 2^21 + 255 * sum < 256 * 2^22 for up to 17 taps (the API's 8x down-scaling limit); the generic tap loops keep `min`.
 constexpr int kS2dPadWords = 4;
 
 template <typename OutT>
@@ -280,11 +285,11 @@ __device__ __forceinline__ void store_cell<__nv_bfloat16>(__nv_bfloat16 *dst, co
 }
 
 template <typename OutT>
-__global__ void __launch_bounds__(kThreads)
+__global__ void __launch_bounds__(kThreads, 5)
 input_s2d_kernel(const uint8_t *__restrict__ images, int64_t image_bytes, const int32_t *__restrict__ boxes,
-                 const uint8_t *__restrict__ flips, OutT *__restrict__ out, const int32_t *__restrict__ ws, int src_h,
-                 int src_w, int out_h, int out_w, int KX, int KY, int max_src_rows, Norm nrm, int src_stride,
-                 int inter_stride) {
+                 const uint8_t *__restrict__ flips, OutT *__restrict__ out, const int32_t *__restrict__ ws,
+                 const float *__restrict__ lut_g, int src_h, int src_w, int out_h, int out_w, int KX, int KY,
+                 int max_src_rows, int src_stride, int inter_stride) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     float *lut = reinterpret_cast<float *>(smem_raw);                        // [3][256]
     uint32_t *src = reinterpret_cast<uint32_t *>(smem_raw + 3 * 256 * sizeof(float));  // [max_src_rows][src_stride]
@@ -295,10 +300,7 @@ input_s2d_kernel(const uint8_t *__restrict__ images, int64_t image_bytes, const 
     const int y0 = ya < 0 ? 0 : ya;
     const int y1 = (ya + kTileRows < out_h) ? ya + kTileRows : out_h;
     const int sy = (out_h + 6) >> 1, sx = (out_w + 6) >> 1;
-    for (int i = threadIdx.x; i < 3 * 256; i += kThreads) {
-        const int ch = i >> 8, v = i & 255;
-        lut[i] = __fdiv_rn(__fsub_rn(__fdiv_rn((float)v, 255.0f), nrm.mean[ch]), nrm.std[ch]);
-    }
+    for (int i = threadIdx.x; i < 3 * 256; i += kThreads) lut[i] = lut_g[i];   // made once by the coefficient kernel
     const int64_t per_sample = (int64_t)out_w * (2 + KX) + (int64_t)out_h * (2 + KY);
     const int32_t *bx = ws + s * per_sample;
     const int32_t *cx = bx + 2 * out_w;
@@ -351,7 +353,8 @@ input_s2d_kernel(const uint8_t *__restrict__ images, int64_t image_bytes, const 
                 const int32_t *k = cx + (int64_t)xx * KX;
                 const uint32_t *px = src + xmin;
                 uint32_t *o = inter + xx + 1;
-                if (cnt <= 4) {
+                const int cmax = __reduce_max_sync(__activemask(), cnt);   // warp-uniform loop bound
+                if (cmax <= 4) {
                     int kk[4];
 #pragma unroll
                     for (int t = 0; t < 4; ++t) kk[t] = (t < cnt) ? k[t] : 0;   // zero taps read the row padding
@@ -359,15 +362,15 @@ input_s2d_kernel(const uint8_t *__restrict__ images, int64_t image_bytes, const 
                         int a0 = 1 << (kPrecisionBits - 1), a1 = a0, a2 = a0;
 #pragma unroll
                         for (int t = 0; t < 4; ++t) {
-                            if (t < 2 || t < cnt) {
+                            if (t < cmax) {
                                 const unsigned w = px[t];
-                                a0 += (int)(w & 0xffu) * kk[t];
-                                a1 += (int)((w >> 8) & 0xffu) * kk[t];
-                                a2 += (int)((w >> 16) & 0xffu) * kk[t];
+                                a0 += (int)__byte_perm(w, 0u, 0x4440) * kk[t];
+                                a1 += (int)__byte_perm(w, 0u, 0x4441) * kk[t];
+                                a2 += (int)__byte_perm(w, 0u, 0x4442) * kk[t];
                             }
                         }
-                        *o = (unsigned)min(a0 >> kPrecisionBits, 255) | ((unsigned)min(a1 >> kPrecisionBits, 255) << 8) |
-                             ((unsigned)min(a2 >> kPrecisionBits, 255) << 16);
+                        *o = (unsigned)(a0 >> kPrecisionBits) | ((unsigned)(a1 >> kPrecisionBits) << 8) |
+                             ((unsigned)(a2 >> kPrecisionBits) << 16);
                     }
                 } else {  // stronger down-scaling: taps stay in memory
                     for (int rr = 0; rr < nrows; ++rr, px += src_stride, o += inter_stride) {
@@ -395,13 +398,15 @@ input_s2d_kernel(const uint8_t *__restrict__ images, int64_t image_bytes, const 
     if (cyy >= sy) return;
     const int yy0 = 2 * cyy - 3;
     OutT *orow = out + (((int64_t)s * sy + cyy) * sx << 4);
-    int ymin[2], ycnt[2];
+    int ymin[2], ycnt[2], ky[2][4];
 #pragma unroll
     for (int r = 0; r < 2; ++r) {
         const int yy = yy0 + r;
         const bool ok = rows_ok && yy >= 0 && yy < out_h;
         ymin[r] = ok ? by[2 * yy] - ylo : 0;
         ycnt[r] = ok ? by[2 * yy + 1] : 0;
+#pragma unroll
+        for (int t = 0; t < 4; ++t) ky[r][t] = (ok && t < ycnt[r]) ? cy[(int64_t)yy * KY + t] : 0;   // row-uniform taps
     }
     for (int cxx = threadIdx.x & 63; cxx < sx; cxx += 64) {
         const int xd0 = 2 * cxx - 3;
@@ -415,32 +420,56 @@ input_s2d_kernel(const uint8_t *__restrict__ images, int64_t image_bytes, const 
 #pragma unroll
             for (int r = 0; r < 2; ++r) {
                 if (ycnt[r] == 0) continue;
-                const int32_t *k = cy + (int64_t)(yy0 + r) * KY;
                 const uint32_t *p = inter + (size_t)ymin[r] * inter_stride + pair;
                 int a[6];
 #pragma unroll
                 for (int i = 0; i < 6; ++i) a[i] = 1 << (kPrecisionBits - 1);
-                for (int t = 0; t < ycnt[r]; ++t, p += inter_stride) {
-                    const int kt = k[t];
-                    const uint2 w = *reinterpret_cast<const uint2 *>(p);
-                    a[0] += (int)(w.x & 0xffu) * kt;
-                    a[1] += (int)((w.x >> 8) & 0xffu) * kt;
-                    a[2] += (int)((w.x >> 16) & 0xffu) * kt;
-                    a[3] += (int)(w.y & 0xffu) * kt;
-                    a[4] += (int)((w.y >> 8) & 0xffu) * kt;
-                    a[5] += (int)((w.y >> 16) & 0xffu) * kt;
+                if (ycnt[r] <= 4) {
+#pragma unroll
+                    for (int t = 0; t < 4; ++t) {
+                        if (t < ycnt[r]) {
+                            const uint2 w = *reinterpret_cast<const uint2 *>(p + (size_t)t * inter_stride);
+                            const int kt = ky[r][t];
+                            a[0] += (int)__byte_perm(w.x, 0u, 0x4440) * kt;
+                            a[1] += (int)__byte_perm(w.x, 0u, 0x4441) * kt;
+                            a[2] += (int)__byte_perm(w.x, 0u, 0x4442) * kt;
+                            a[3] += (int)__byte_perm(w.y, 0u, 0x4440) * kt;
+                            a[4] += (int)__byte_perm(w.y, 0u, 0x4441) * kt;
+                            a[5] += (int)__byte_perm(w.y, 0u, 0x4442) * kt;
+                        }
+                    }
+                } else {
+                    const int32_t *k = cy + (int64_t)(yy0 + r) * KY;
+                    for (int t = 0; t < ycnt[r]; ++t, p += inter_stride) {
+                        const int kt = k[t];
+                        const uint2 w = *reinterpret_cast<const uint2 *>(p);
+                        a[0] += (int)(w.x & 0xffu) * kt;
+                        a[1] += (int)((w.x >> 8) & 0xffu) * kt;
+                        a[2] += (int)((w.x >> 16) & 0xffu) * kt;
+                        a[3] += (int)(w.y & 0xffu) * kt;
+                        a[4] += (int)((w.y >> 8) & 0xffu) * kt;
+                        a[5] += (int)((w.y >> 16) & 0xffu) * kt;
+                    }
                 }
-                // a[0..2] = lower source column, a[3..5] = upper; destination order swaps them when flipping
+                // a[0..2] = lower source column, a[3..5] = upper; destination order swaps them when flipping.
+                // No clamp: see the note above the kernel (the sum is provably < 256 << 22 and >= 0).
 #pragma unroll
                 for (int ch = 0; ch < 3; ++ch) {
                     const int e0 = flip ? a[3 + ch] : a[ch], e1 = flip ? a[ch] : a[3 + ch];
-                    if (v0) f[r * 6 + ch] = lut[ch * 256 + min(e0 >> kPrecisionBits, 255)];
-                    if (v1) f[r * 6 + 3 + ch] = lut[ch * 256 + min(e1 >> kPrecisionBits, 255)];
+                    if (v0) f[r * 6 + ch] = lut[ch * 256 + (e0 >> kPrecisionBits)];
+                    if (v1) f[r * 6 + 3 + ch] = lut[ch * 256 + (e1 >> kPrecisionBits)];
                 }
             }
         }
         store_cell<OutT>(orow + ((int64_t)cxx << 4), f);
     }
+}
+
+// Ask for the largest shared-memory carve-out, so that shared memory does not cap the resident CTAs below what the
+// registers allow (a per-device function attribute: set on every call, it is a cheap host-side operation).
+template <typename K>
+cudaError_t prefer_shared(K kern) {
+    return cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
 }
 
 int max_src_rows_for(int src_h, int out_h) {
@@ -454,7 +483,8 @@ int max_src_rows_for(int src_h, int out_h) {
 extern "C" size_t b200_input_workspace_bytes(int64_t n, int src_h, int src_w, int out_h, int out_w) {
     if (n < 1 || src_h < 1 || src_w < 1 || out_h < 1 || out_w < 1) return 0;
     const int KX = ksize_for(src_w, out_w), KY = ksize_for(src_h, out_h);
-    return sizeof(int32_t) * (size_t)n * ((size_t)out_w * (2 + KX) + (size_t)out_h * (2 + KY)) + 16;
+    // per-sample coefficient tables, then the 3x256 float normalisation table
+    return sizeof(int32_t) * (size_t)n * ((size_t)out_w * (2 + KX) + (size_t)out_h * (2 + KY)) + 3 * 256 * sizeof(float) + 16;
 }
 
 extern "C" int b200_input_crop_resize_flip_norm(const uint8_t *images, const int32_t *boxes, const uint8_t *flips,
@@ -475,8 +505,12 @@ extern "C" int b200_input_crop_resize_flip_norm(const uint8_t *images, const int
     const int KX = ksize_for(src_w, out_w), KY = ksize_for(src_h, out_h);
     int32_t *ws = static_cast<int32_t *>(workspace);
     const int64_t items = n * (int64_t)(out_w + out_h);
-    input_coeff_kernel<<<(unsigned)((items + kThreads - 1) / kThreads), kThreads, 0, st>>>(boxes, n, out_h, out_w, KX,
-                                                                                           KY, ws);
+    float *lut_g = reinterpret_cast<float *>(ws + n * ((int64_t)out_w * (2 + KX) + (int64_t)out_h * (2 + KY)));
+    Norm nrm0;
+    for (int i = 0; i < 3; ++i) { nrm0.mean[i] = mean3[i]; nrm0.std[i] = std3[i]; }
+    const int64_t items_l = items > 3 * 256 ? items : 3 * 256;
+    input_coeff_kernel<<<(unsigned)((items_l + kThreads - 1) / kThreads), kThreads, 0, st>>>(boxes, n, out_h, out_w, KX,
+                                                                                             KY, ws, lut_g, nrm0);
     B200_CHECK_LAUNCH();
     const int max_rows = max_src_rows_for(src_h, out_h);
     const size_t esz = out_dtype == B200_F32 ? 4 : 2;
@@ -484,23 +518,23 @@ extern "C" int b200_input_crop_resize_flip_norm(const uint8_t *images, const int
         const int src_stride = (src_w + kS2dPadWords + 3) / 4 * 4, inter_stride = out_w + 2;
         const size_t smem2 = 3 * 256 * sizeof(float) + (size_t)max_rows * (src_stride + inter_stride) * sizeof(uint32_t);
         if (smem2 <= 96 * 1024) {   // larger boxes / stronger down-scaling use the generic kernel below
-            Norm nrm2;
-            for (int i = 0; i < 3; ++i) { nrm2.mean[i] = mean3[i]; nrm2.std[i] = std3[i]; }
             const dim3 grid2((out_h + 6 + kTileRows - 1) / kTileRows, (unsigned)n);
             const int64_t image_bytes = n * (int64_t)src_h * src_w * 3;
             cudaError_t e = cudaSuccess;
             if (out_dtype == B200_F32) {
                 auto kern = input_s2d_kernel<float>;
                 if (smem2 > 48 * 1024) e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2);
+                if (e == cudaSuccess) e = prefer_shared(kern);
                 if (e != cudaSuccess) return (int)e;
-                kern<<<grid2, kThreads, smem2, st>>>(images, image_bytes, boxes, flips, static_cast<float *>(out), ws, src_h,
-                                                     src_w, out_h, out_w, KX, KY, max_rows, nrm2, src_stride, inter_stride);
+                kern<<<grid2, kThreads, smem2, st>>>(images, image_bytes, boxes, flips, static_cast<float *>(out), ws, lut_g,
+                                                     src_h, src_w, out_h, out_w, KX, KY, max_rows, src_stride, inter_stride);
             } else {
                 auto kern = input_s2d_kernel<__nv_bfloat16>;
                 if (smem2 > 48 * 1024) e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2);
+                if (e == cudaSuccess) e = prefer_shared(kern);
                 if (e != cudaSuccess) return (int)e;
                 kern<<<grid2, kThreads, smem2, st>>>(images, image_bytes, boxes, flips, static_cast<__nv_bfloat16 *>(out), ws,
-                                                     src_h, src_w, out_h, out_w, KX, KY, max_rows, nrm2, src_stride,
+                                                     lut_g, src_h, src_w, out_h, out_w, KX, KY, max_rows, src_stride,
                                                      inter_stride);
             }
             B200_CHECK_LAUNCH();
