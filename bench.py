@@ -24,6 +24,13 @@ sys.path.insert(0, ROOT)
 METRIC = "ResNet-50 train images/sec"
 
 
+def metric_name(a):
+    """BASELINE.json's metric for the default architecture; other --arch runs say which network they timed."""
+    if a.arch == "resnet50":
+        return METRIC
+    return "ResNet-" + a.arch[len("resnet"):] + " train images/sec"
+
+
 def parse():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -125,7 +132,7 @@ def run_reference(a):
     r = train_cpu.time_reference_step(a.arch, a.ref_batch, a.image, a.steps, a.warmup)
     v = r["images_per_sec"]
     print(json.dumps({
-        "impl": "reference", "metric": METRIC, "value": v, "unit": "images/s", "n_gpus": a.gpus, "steps": a.steps,
+        "impl": "reference", "metric": metric_name(a), "value": v, "unit": "images/s", "n_gpus": a.gpus, "steps": a.steps,
         "warmup": a.warmup, "ms_per_step": r["ms_per_step"], "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": workload_name(a), "reference_arm": "CPU restatement of train() (oracle port), "
@@ -187,7 +194,7 @@ def run_eager(a):
     if world > 1:
         dist.all_reduce(ms, op=dist.ReduceOp.MAX)
     if rank == 0:
-        print(json.dumps({"impl": "eager", "metric": METRIC, "value": a.batch * world * a.steps / (float(ms) / 1e3),
+        print(json.dumps({"impl": "eager", "metric": metric_name(a), "value": a.batch * world * a.steps / (float(ms) / 1e3),
                           "unit": "images/s", "n_gpus": world, "steps": a.steps, "warmup": a.warmup,
                           "ms_per_step": float(ms) / a.steps, "higher_is_better": True, "scaling": "weak",
                           "dtype": "bf16 autocast, channels_last" if a.eager_amp else "f32 NCHW (as the reference)",
@@ -457,7 +464,7 @@ def run_ours(a):
             except Exception as e:  # noqa: BLE001
                 notes.append(f"cpu_baseline failed: {type(e).__name__}: {str(e)[:200]}")
         out = {
-            "metric": METRIC, "value": value, "unit": "images/s", "n_gpus": world, "steps": a.steps,
+            "metric": metric_name(a), "value": value, "unit": "images/s", "n_gpus": world, "steps": a.steps,
             "warmup": a.warmup, "ms_per_step": ms_total / a.steps, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f32" if a.fp32 else "bf16", "data": "synthetic",
             "config": {"workload": workload_name(a), "arch": a.arch, "per_gpu_batch": a.batch,
