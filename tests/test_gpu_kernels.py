@@ -600,3 +600,36 @@ def test_maxpool_and_pack_write_only_inside_their_outputs():
         touched[o:o + t.numel()] = True
         assert torch.equal(dst[o:o + t.numel()], t.float())
     assert bool((dst[~touched] == -7.0).all())
+
+
+@pytest.mark.parametrize("layout", [cabi.LAYOUT_S2D_STEM, cabi.LAYOUT_NHWC])
+def test_input_stage_writes_only_inside_its_output_and_workspace(layout):
+    """Guard bands around the output and the coefficient workspace of the input stage (both kernels of the stem
+    layout write whole cells / tables with vector stores)."""
+    import ctypes
+
+    lib = cabi.load()
+    n, sh, sw, oh, ow = 5, 61, 83, 40, 36
+    g = torch.Generator().manual_seed(5)
+    images = torch.randint(0, 256, (n, sh, sw, 3), dtype=torch.uint8, generator=g).to(DEV)
+    from imagent_distributed_training_pytorch_with_slurm_b200.data import draw_batch_params
+    boxes, flips = draw_batch_params(n, sh, sw, g)
+    boxes, flips = boxes.to(DEV), flips.to(DEV)
+    out_elems = n * ((oh + 6) // 2) * ((ow + 6) // 2) * 16 if layout == cabi.LAYOUT_S2D_STEM else n * oh * ow * 3
+    ws_bytes = lib.b200_input_workspace_bytes(n, sh, sw, oh, ow)
+    sizes = {"out": out_elems * 2, "ws": ws_bytes}
+    bufs = {k: _guarded(v) for k, v in sizes.items()}
+    ptr = lambda k: bufs[k][0].data_ptr() + bufs[k][1]
+    f3 = ctypes.c_float * 3
+    rc = lib.b200_input_crop_resize_flip_norm(images.data_ptr(), boxes.data_ptr(), flips.data_ptr(), ptr("out"), ptr("ws"),
+                                              ws_bytes, n, sh, sw, oh, ow, f3(.485, .456, .406), f3(.229, .224, .225),
+                                              cabi.BF16, layout, torch.cuda.current_stream().cuda_stream)
+    assert rc == 0
+    torch.cuda.synchronize()
+    for k, (whole, pad) in bufs.items():
+        assert _guards_intact(whole, pad, sizes[k]), k
+    # and the guarded call produced the same image as the wrapper
+    want = cabi.input_stage(images, boxes, flips, oh, ow, (.485, .456, .406), (.229, .224, .225), torch.bfloat16, layout)
+    got = bufs["out"][0][bufs["out"][1]:bufs["out"][1] + sizes["out"]].view(torch.bfloat16)
+    ref = want.permute(0, 2, 3, 1).contiguous().view(-1) if layout != cabi.LAYOUT_NCHW else want.view(-1)
+    assert torch.equal(got, ref)
