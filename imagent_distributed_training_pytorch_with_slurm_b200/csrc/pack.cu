@@ -11,21 +11,36 @@ namespace {
 constexpr int kThreads = 256;
 constexpr int kMaxTensors = 64;
 
+constexpr int kBlockElems = kThreads * 8 * 4;   // elements one CTA converts: 4 steps of 8 per thread (16 KB in, 32 KB out)
+
 struct PackTable {
     const void *src[kMaxTensors];
     long long off[kMaxTensors];
     long long cnt[kMaxTensors];
+    int first_block[kMaxTensors + 1];   // prefix sum of ceil(cnt / kBlockElems): CTAs are dealt out in proportion to size
 };
 
+// The first version gave every tensor the same 32 CTAs: the 9.4 MB tensors of layer4 set the duration while the CTAs
+// of the small ones idled (3.5 TB/s).  Now the grid is flat over all tensors' 8192-element blocks and a CTA finds its
+// tensor by binary search in the prefix table (kernel parameter space = constant bank, uniform across the CTA).
 template <typename T>
-__global__ void __launch_bounds__(kThreads) pack_grads_kernel(const __grid_constant__ PackTable tab,
+__global__ void __launch_bounds__(kThreads) pack_grads_kernel(const __grid_constant__ PackTable tab, int n_tensors,
                                                               float *__restrict__ dst, float scale) {
-    const int t = blockIdx.y;
+    int lo = 0, hi = n_tensors;   // largest t with first_block[t] <= blockIdx.x
+    while (hi - lo > 1) {
+        const int mid = (lo + hi) >> 1;
+        if (tab.first_block[mid] <= (int)blockIdx.x) lo = mid; else hi = mid;
+    }
+    const int t = lo;
     const T *src = static_cast<const T *>(tab.src[t]);
     float *out = dst + tab.off[t];
     const long long n = tab.cnt[t];
     const long long n8 = n >> 3;
-    for (long long v = (long long)blockIdx.x * kThreads + threadIdx.x; v < n8; v += (long long)gridDim.x * kThreads) {
+    const long long v0 = (long long)((int)blockIdx.x - tab.first_block[t]) * (kBlockElems / 8);
+#pragma unroll
+    for (int step = 0; step < kBlockElems / 8 / kThreads; ++step) {
+        const long long v = v0 + step * kThreads + threadIdx.x;
+        if (v >= n8) break;
         float e[8];
         if constexpr (sizeof(T) == 2) {
             VecIO<__nv_bfloat16, 8>::load(reinterpret_cast<const __nv_bfloat16 *>(src) + v * 8, e);
@@ -41,7 +56,7 @@ __global__ void __launch_bounds__(kThreads) pack_grads_kernel(const __grid_const
         VecIO<float, 4>::store(out + v * 8, a);
         VecIO<float, 4>::store(out + v * 8 + 4, b);
     }
-    if (blockIdx.x == 0 && threadIdx.x < (n & 7)) {
+    if ((int)blockIdx.x == tab.first_block[t] && threadIdx.x < (n & 7)) {   // ragged tail, by the tensor's first CTA
         const long long i = (n8 << 3) + threadIdx.x;
         float v;
         if constexpr (sizeof(T) == 2) v = __bfloat162float(reinterpret_cast<const __nv_bfloat16 *>(src)[i]);
@@ -60,23 +75,25 @@ extern "C" int b200_pack_grads(const void *const *srcs, const int64_t *offsets, 
     for (int base = 0; base < n_tensors; base += kMaxTensors) {
         const int m = n_tensors - base < kMaxTensors ? n_tensors - base : kMaxTensors;
         PackTable tab;
-        long long biggest = 0;
+        long long blocks = 0;
         for (int i = 0; i < m; ++i) {
             if (!srcs[base + i] || offsets[base + i] < 0 || counts[base + i] < 0) return (int)cudaErrorInvalidValue;
             if (b200_misaligned(srcs[base + i]) || (offsets[base + i] & 3)) return (int)cudaErrorMisalignedAddress;
             tab.src[i] = srcs[base + i];
             tab.off[i] = offsets[base + i];
             tab.cnt[i] = counts[base + i];
-            if (counts[base + i] > biggest) biggest = counts[base + i];
+            tab.first_block[i] = (int)blocks;
+            const long long nb = (counts[base + i] + kBlockElems - 1) / kBlockElems;
+            blocks += nb > 0 ? nb : 1;   // an empty tensor keeps one (idle) CTA so that the search stays well-defined
+            if (blocks > 0x7fffffffLL) return (int)cudaErrorInvalidValue;
         }
         for (int i = m; i < kMaxTensors; ++i) { tab.src[i] = nullptr; tab.off[i] = 0; tab.cnt[i] = 0; }
+        for (int i = m; i <= kMaxTensors; ++i) tab.first_block[i] = (int)blocks;
         if (b200_misaligned(dst)) return (int)cudaErrorMisalignedAddress;
-        long long bx = (biggest / 8 + kThreads - 1) / kThreads;
-        if (bx < 1) bx = 1;
-        if (bx > 32) bx = 32;
-        const dim3 grid((unsigned)bx, (unsigned)m);
-        if (src_dtype == B200_BF16) pack_grads_kernel<__nv_bfloat16><<<grid, kThreads, 0, st>>>(tab, dst, scale);
-        else pack_grads_kernel<float><<<grid, kThreads, 0, st>>>(tab, dst, scale);
+        if (src_dtype == B200_BF16)
+            pack_grads_kernel<__nv_bfloat16><<<(unsigned)blocks, kThreads, 0, st>>>(tab, m, dst, scale);
+        else
+            pack_grads_kernel<float><<<(unsigned)blocks, kThreads, 0, st>>>(tab, m, dst, scale);
         B200_CHECK_LAUNCH();
     }
     return 0;
