@@ -16,7 +16,7 @@ LIB_PATH = os.path.join(_HERE, "libb200_imagenet.so")
 F32, BF16 = 0, 1
 ACT_NONE, ACT_RELU, ACT_ADD_RELU = 0, 1, 2
 LAYOUT_NHWC, LAYOUT_NCHW, LAYOUT_S2D_STEM = 0, 1, 2
-ABI_VERSION = 1
+ABI_VERSION = 2
 
 _c = ctypes
 _vp, _i64, _i32, _f32, _sz = _c.c_void_p, _c.c_int64, _c.c_int, _c.c_float, _c.c_size_t
@@ -38,7 +38,7 @@ SIGNATURES = {
     "b200_bn_fwd_eval": (_i32, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _i64, _i32, _f32, _i32, _i32, _vp]),
     "b200_bn_bwd": (_i32, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _sz, _i64, _i32, _i32, _i32, _vp]),
     "b200_maxpool3x3s2_fwd": (_i32, [_vp, _vp, _vp, _i64, _i32, _i32, _i32, _i32, _vp]),
-    "b200_maxpool3x3s2_bwd": (_i32, [_vp, _vp, _vp, _i64, _i32, _i32, _i32, _i32, _vp]),
+    "b200_maxpool3x3s2_bwd": (_i32, [_vp, _vp, _vp, _vp, _i64, _i32, _i32, _i32, _i32, _vp]),
     "b200_bn_dual_supported": (_i32, [_i32, _i32]),
     "b200_bn_stats": (_i32, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _sz, _i64, _i32, _f32, _f32, _i32, _vp]),
     "b200_bn_fwd_train_dual": (_i32, [_vp] * 12 + [_sz, _i64, _i32, _f32, _f32, _i32, _vp]),
@@ -450,16 +450,21 @@ def maxpool_fwd(x):
     return y, arg
 
 
-def maxpool_bwd(dy, arg, in_shape):
-    _need_cuda(dy, arg)
+def maxpool_bwd(dy, arg, in_shape, dy2=None):
+    """dx of the 3x3/2/1 max-pool; ``dy2`` (same shape as dy) is a second gradient branch summed on the fly."""
+    _need_cuda(dy, arg, dy2)
     n, c, h, w = in_shape
     if not dy.is_contiguous(memory_format=torch.channels_last):
         raise B200Error("max-pool kernel needs a channels-last gradient")
+    if dy2 is not None and (dy2.shape != dy.shape or dy2.dtype != dy.dtype
+                            or not dy2.is_contiguous(memory_format=torch.channels_last)):
+        raise B200Error("max-pool kernel: the second gradient must match the first (shape, dtype, channels-last)")
     dx = torch.empty((n, c, h, w), dtype=dy.dtype, device=dy.device, memory_format=torch.channels_last)
     s = stats.begin("maxpool_bwd")
-    _check(load().b200_maxpool3x3s2_bwd(_ptr(dy), _ptr(arg), _ptr(dx), n, c, h, w, dtype_code(dy), _stream()),
+    _check(load().b200_maxpool3x3s2_bwd(_ptr(dy), _ptr(dy2), _ptr(arg), _ptr(dx), n, c, h, w, dtype_code(dy), _stream()),
            "b200_maxpool3x3s2_bwd")
-    stats.end("maxpool_bwd", 1, s, dx.numel() * dx.element_size() + dy.numel() * (dy.element_size() + 1))
+    stats.end("maxpool_bwd", 1, s, dx.numel() * dx.element_size() + dy.numel() * (dy.element_size() + 1)
+              + (dy2.numel() * dy2.element_size() if dy2 is not None else 0))
     return dx
 
 

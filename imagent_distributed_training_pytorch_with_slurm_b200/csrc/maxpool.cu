@@ -86,8 +86,8 @@ maxpool_fwd_kernel(const T *__restrict__ x, T *__restrict__ y, uint8_t *__restri
 // produces four output vectors.
 template <typename T>
 __global__ void __launch_bounds__(kThreads)
-maxpool_bwd_kernel(const T *__restrict__ dy, const uint8_t *__restrict__ arg, T *__restrict__ dx, int64_t total, int c8,
-                   int h, int w, int oh, int ow) {
+maxpool_bwd_kernel(const T *__restrict__ dy, const T *__restrict__ dy2, const uint8_t *__restrict__ arg,
+                   T *__restrict__ dx, int64_t total, int c8, int h, int w, int oh, int ow) {
     const int64_t gid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (gid >= total) return;
     const int ph = (h + 1) >> 1, pw = (w + 1) >> 1;
@@ -108,6 +108,12 @@ maxpool_bwd_kernel(const T *__restrict__ dy, const uint8_t *__restrict__ arg, T 
                 const int64_t o = (((n * oh + oy) * ow + ox) * c8 + cv) * 8;
                 const uint2 p = *reinterpret_cast<const uint2 *>(arg + o);
                 V8<T>::load(dy + o, g[a][b]);
+                if (dy2) {
+                    float g2[8];
+                    V8<T>::load(dy2 + o, g2);
+#pragma unroll
+                    for (int k = 0; k < 8; ++k) g[a][b][k] += g2[k];
+                }
 #pragma unroll
                 for (int k = 0; k < 8; ++k) pos[a][b][k] = ((k < 4 ? p.x : p.y) >> ((k & 3) * 8)) & 0xffu;
             } else {
@@ -251,9 +257,9 @@ maxpool_fwd_bf16_kernel(const __nv_bfloat16 *__restrict__ x, __nv_bfloat16 *__re
 // bytes and gradients of a window are unpacked once and compared against the position each pixel of the patch has in
 // that window (one compare + one predicated add per contribution).
 __global__ void __launch_bounds__(kThreads, 3)
-maxpool_bwd_bf16_kernel(const __nv_bfloat16 *__restrict__ dy, const uint8_t *__restrict__ arg,
-                        __nv_bfloat16 *__restrict__ dx, unsigned total, FastDiv dc8, FastDiv dpw, FastDiv dph, int h,
-                        int w, int oh, int ow) {
+maxpool_bwd_bf16_kernel(const __nv_bfloat16 *__restrict__ dy, const __nv_bfloat16 *__restrict__ dy2,
+                        const uint8_t *__restrict__ arg, __nv_bfloat16 *__restrict__ dx, unsigned total, FastDiv dc8,
+                        FastDiv dpw, FastDiv dph, int h, int w, int oh, int ow) {
     const unsigned gid = blockIdx.x * kThreads + threadIdx.x;
     if (gid >= total) return;
     const int c8 = (int)dc8.d;
@@ -263,21 +269,24 @@ maxpool_bwd_bf16_kernel(const __nv_bfloat16 *__restrict__ dy, const uint8_t *__r
     const int px = (int)(r - q * dpw.d);
     const unsigned n = fdiv(q, dph);
     const int py = (int)(q - n * dph.d);
-    uint4 g[2][2];
+    uint4 g[2][2], g2[2][2];
     uint2 p[2][2];
     const unsigned o00 = ((n * (unsigned)oh + py) * ow + px) * c8 + cv;  // < total: fits 32 bits
     const uint2 *ap = reinterpret_cast<const uint2 *>(arg) + o00;
     const uint4 *gp = reinterpret_cast<const uint4 *>(dy) + o00;
+    const uint4 *gp2 = dy2 ? reinterpret_cast<const uint4 *>(dy2) + o00 : nullptr;   // second gradient branch (fan-in)
 #pragma unroll
     for (int a = 0; a < 2; ++a)
 #pragma unroll
         for (int b = 0; b < 2; ++b) {
             p[a][b] = make_uint2(0xffffffffu, 0xffffffffu);
             g[a][b] = make_uint4(0u, 0u, 0u, 0u);
+            g2[a][b] = make_uint4(0u, 0u, 0u, 0u);
             if (py + a < oh && px + b < ow) {
                 const int off = (a * ow + b) * c8;
                 p[a][b] = __ldg(ap + off);
                 g[a][b] = __ldg(gp + off);
+                if (gp2) g2[a][b] = __ldg(gp2 + off);
             }
         }
     float acc[2][2][8];
@@ -292,10 +301,12 @@ maxpool_bwd_bf16_kernel(const __nv_bfloat16 *__restrict__ dy, const uint8_t *__r
 #pragma unroll
         for (int b = 0; b < 2; ++b) {
             const unsigned gw[4] = {g[a][b].x, g[a][b].y, g[a][b].z, g[a][b].w};
+            const unsigned hw[4] = {g2[a][b].x, g2[a][b].y, g2[a][b].z, g2[a][b].w};
 #pragma unroll
             for (int k = 0; k < 8; ++k) {
                 const unsigned pk = __byte_perm(k < 4 ? p[a][b].x : p[a][b].y, 0u, 0x4440u | (k & 3));
-                const float f = __uint_as_float((k & 1) ? (gw[k >> 1] & 0xffff0000u) : (gw[k >> 1] << 16));
+                float f = __uint_as_float((k & 1) ? (gw[k >> 1] & 0xffff0000u) : (gw[k >> 1] << 16));
+                if (gp2) f += __uint_as_float((k & 1) ? (hw[k >> 1] & 0xffff0000u) : (hw[k >> 1] << 16));
 #pragma unroll
                 for (int i = 0; i < 2; ++i) {
                     const int kh = i + 1 - 2 * a;
@@ -354,26 +365,30 @@ extern "C" int b200_maxpool3x3s2_fwd(const void *x, void *y, uint8_t *argmax, in
     return 0;
 }
 
-extern "C" int b200_maxpool3x3s2_bwd(const void *dy, const uint8_t *argmax, void *dx, int64_t n, int c, int h, int w,
-                                     int dtype, void *stream) {
+extern "C" int b200_maxpool3x3s2_bwd(const void *dy, const void *dy2, const uint8_t *argmax, void *dx, int64_t n, int c,
+                                     int h, int w, int dtype, void *stream) {
     if (!dy || !dx || !argmax || n < 1 || c < 8 || (c % 8) || h < 1 || w < 1) return (int)cudaErrorInvalidValue;
     if (dtype != B200_F32 && dtype != B200_BF16) return (int)cudaErrorInvalidValue;
-    if (b200_misaligned(dy) || b200_misaligned(dx) || b200_misaligned(argmax, 8)) return (int)cudaErrorMisalignedAddress;
+    if (b200_misaligned(dy) || b200_misaligned(dx) || b200_misaligned(argmax, 8) || (dy2 && b200_misaligned(dy2)))
+        return (int)cudaErrorMisalignedAddress;
     const int oh = (h + 2 - 3) / 2 + 1, ow = (w + 2 - 3) / 2 + 1;
     const int64_t total = n * ((h + 1) / 2) * ((w + 1) / 2) * (c / 8);
     const unsigned blocks = (unsigned)((total + kThreads - 1) / kThreads);
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     if (dtype == B200_BF16 && total < (1ll << 31))
-        maxpool_bwd_bf16_kernel<<<blocks, kThreads, 0, st>>>(static_cast<const __nv_bfloat16 *>(dy), argmax,
+        maxpool_bwd_bf16_kernel<<<blocks, kThreads, 0, st>>>(static_cast<const __nv_bfloat16 *>(dy),
+                                                            static_cast<const __nv_bfloat16 *>(dy2), argmax,
                                                             static_cast<__nv_bfloat16 *>(dx), (unsigned)total,
                                                             make_fastdiv(c / 8), make_fastdiv((w + 1) / 2),
                                                             make_fastdiv((h + 1) / 2), h, w, oh, ow);
     else if (dtype == B200_BF16)
-        maxpool_bwd_kernel<__nv_bfloat16><<<blocks, kThreads, 0, st>>>(static_cast<const __nv_bfloat16 *>(dy), argmax,
+        maxpool_bwd_kernel<__nv_bfloat16><<<blocks, kThreads, 0, st>>>(static_cast<const __nv_bfloat16 *>(dy),
+                                                                      static_cast<const __nv_bfloat16 *>(dy2), argmax,
                                                                       static_cast<__nv_bfloat16 *>(dx), total, c / 8, h,
                                                                       w, oh, ow);
     else
-        maxpool_bwd_kernel<float><<<blocks, kThreads, 0, st>>>(static_cast<const float *>(dy), argmax,
+        maxpool_bwd_kernel<float><<<blocks, kThreads, 0, st>>>(static_cast<const float *>(dy),
+                                                              static_cast<const float *>(dy2), argmax,
                                                               static_cast<float *>(dx), total, c / 8, h, w, oh, ow);
     B200_CHECK_LAUNCH();
     return 0;

@@ -120,15 +120,27 @@ class _StemS2D:
                 or tuple(conv.dilation) != (1, 1) or conv.groups != 1):
             raise ValueError("space-to-depth stem needs the torchvision 7x7/2/3 RGB stem")
         self.conv, self.arena, self._w, self._at = conv, arena, None, -1
+        self._flat, self._idx = None, None
+
+    def _gather_index(self, k, device):
+        """int64 [K,16,4,4] (channels-last): for every element of the rearranged weight, its position in the flat
+        [K,3,7,7] weight, or K*147 (a slot that holds zero) for the padded taps and the 4 spare channels."""
+        zero = k * 147
+        src = torch.arange(zero, dtype=torch.int64).reshape(k, 3, 7, 7)
+        w8 = torch.nn.functional.pad(src, (0, 1, 0, 1), value=zero)                 # [K,3,8,8]
+        w = w8.reshape(k, 3, 4, 2, 4, 2).permute(0, 3, 5, 1, 2, 4)                 # K, dy, dx, ch, R, S
+        w = torch.nn.functional.pad(w.reshape(k, 12, 4, 4), (0, 0, 0, 0, 0, 4), value=zero)
+        return w.contiguous(memory_format=torch.channels_last).to(device)
 
     def weight(self):
         if self._at != self.arena.steps or self._w is None:
             w7 = self.conv.w_compute
             k = w7.shape[0]
-            w8 = torch.nn.functional.pad(w7, (0, 1, 0, 1))                       # [K,3,8,8]
-            w = w8.reshape(k, 3, 4, 2, 4, 2).permute(0, 3, 5, 1, 2, 4)           # K, dy, dx, ch, R, S
-            w = torch.nn.functional.pad(w.reshape(k, 12, 4, 4), (0, 0, 0, 0, 0, 4))
-            self._w, self._at = w.contiguous(memory_format=torch.channels_last), self.arena.steps
+            if self._idx is None or self._idx.device != w7.device or self._flat.dtype != w7.dtype:
+                self._idx = self._gather_index(k, w7.device)
+                self._flat = torch.zeros(k * 147 + 1, dtype=w7.dtype, device=w7.device)   # last slot stays zero
+            self._flat[:-1].view(k, 3, 7, 7).copy_(w7)                                   # 1 kernel
+            self._w, self._at = self._flat[self._idx], self.arena.steps                   # 1 kernel (gather)
         return self._w
 
     def fwd(self, x):
@@ -488,15 +500,17 @@ class B200ResNet(nn.Module):
             fc.g_bias.copy_(g_logits.sum(0, dtype=torch.float32) * pre)
         self._progress(self._marks["fc"])
         n, c, h, w = tape.pop("last_shape")
-        g = (g_feat * (1.0 / (h * w))).view(n, c, 1, 1).expand(n, c, h, w).contiguous(memory_format=torch.channels_last)
+        # gradient of the global average pool: one row of C values repeated over the H*W positions (channels-last, so
+        # the copy moves whole rows)
+        g = (g_feat * (1.0 / (h * w))).view(n, 1, 1, c).expand(n, h, w, c).contiguous().permute(0, 3, 1, 2)
         blocks = tape.pop("blocks")
         for li in range(4, 0, -1):
             layer = getattr(self, f"layer{li}")
             for bi in range(len(layer) - 1, -1, -1):
                 g = layer[bi].bwd(g, blocks.pop())
                 self._progress(self._marks[(li, bi)])
-        g = g[0].add_(g[1])  # the stem has no BatchNorm behind the first block to absorb the sum
-        g = _cabi.maxpool_bwd(g, tape.pop("pool_idx"), tape.pop("pool_in_shape"))
+        # the two gradient branches of the first block meet at the pooled tensor: the pool's backward sums them
+        g = _cabi.maxpool_bwd(g[0], tape.pop("pool_idx"), tape.pop("pool_in_shape"), g[1])
         g, _ = self.bn1.bwd(g, tape.pop("t1"), tape.pop("saved1"), None, _cabi.ACT_RELU)
         stem = tape.pop("stem")
         if stem is self.conv1:

@@ -27,7 +27,7 @@
 extern "C" {
 #endif
 
-#define B200_ABI_VERSION 1
+#define B200_ABI_VERSION 2
 
 enum { B200_F32 = 0, B200_BF16 = 1 };
 enum { B200_ACT_NONE = 0, B200_ACT_RELU = 1, B200_ACT_ADD_RELU = 2 };
@@ -229,11 +229,14 @@ int b200_input_crop_resize_flip_norm(const uint8_t *images, const int32_t *boxes
  *            maximum wins, NaN counts as maximum (ATen's rule)
  *   backward: dx[n,h,w,c] = sum of dy over the (at most 4) windows whose argmax is that pixel,
  *            accumulated in float32; every element of dx is written (no zero-fill needed).
+ *            dy2 (may be NULL): a second gradient of the same shape that is added to dy on the fly - the
+ *            fan-in sum autograd performs where the pooled tensor feeds both branches of the first
+ *            residual block (torchvision resnet.py:143-161,240-243), without a separate add kernel.
  */
 int b200_maxpool3x3s2_fwd(const void *x, void *y, uint8_t *argmax, int64_t n, int c, int h, int w, int dtype,
                           void *stream);
-int b200_maxpool3x3s2_bwd(const void *dy, const uint8_t *argmax, void *dx, int64_t n, int c, int h, int w, int dtype,
-                          void *stream);
+int b200_maxpool3x3s2_bwd(const void *dy, const void *dy2, const uint8_t *argmax, void *dx, int64_t n, int c, int h,
+                          int w, int dtype, void *stream);
 
 /* ------------------------------------------------------------------------------------------------
  * K5  gradient packing: many weight-gradient tensors -> their slots of one flat float32 buffer.

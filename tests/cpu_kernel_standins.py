@@ -113,8 +113,11 @@ def maxpool_fwd(x):
     return torch.from_numpy(y).to(x.dtype).permute(0, 3, 1, 2), torch.from_numpy(pos)
 
 
-def maxpool_bwd(dy, arg, in_shape):
-    dx = omp.maxpool3x3s2_bwd_oracle(dy.permute(0, 2, 3, 1).float().numpy(), arg.numpy(), (in_shape[2], in_shape[3]))
+def maxpool_bwd(dy, arg, in_shape, dy2=None):
+    g = dy.permute(0, 2, 3, 1).float().numpy()
+    if dy2 is not None:
+        g = g + dy2.permute(0, 2, 3, 1).float().numpy()
+    dx = omp.maxpool3x3s2_bwd_oracle(g, arg.numpy(), (in_shape[2], in_shape[3]))
     return torch.from_numpy(dx).to(dy.dtype).permute(0, 3, 1, 2)
 
 

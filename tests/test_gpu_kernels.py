@@ -365,6 +365,15 @@ def test_maxpool_matches_oracle(shape, dtype):
         assert np.allclose(got, dxo, rtol=1e-6, atol=1e-6)
     else:
         assert np.abs(got - dxo).max() <= np.abs(dxo).max() * 2 ** -8 + 1e-9
+    # fan-in: a second gradient branch is summed on the fly (float32 sum, no intermediate rounding)
+    dy2 = torch.randn(yo.shape, generator=g).to(dtype)
+    dx2 = cabi.maxpool_bwd(dy.to(DEV).permute(0, 3, 1, 2), arg, xd.shape, dy2.to(DEV).permute(0, 3, 1, 2))
+    dxo2 = omp.maxpool3x3s2_bwd_oracle(dy.float().numpy() + dy2.float().numpy(), pos, (h, w))
+    got2 = dx2.float().cpu().permute(0, 2, 3, 1).numpy()
+    if dtype == torch.float32:
+        assert np.allclose(got2, dxo2, rtol=1e-6, atol=1e-6)
+    else:
+        assert np.abs(got2 - dxo2).max() <= np.abs(dxo2).max() * 2 ** -8 + 1e-9
 
 
 def test_maxpool_bf16_packed_path_follows_the_scalar_rule_with_nan_inf_and_signed_zero():
@@ -583,7 +592,7 @@ def test_maxpool_and_pack_write_only_inside_their_outputs():
     ptr = lambda k: bufs[k][0].data_ptr() + bufs[k][1]
     st = torch.cuda.current_stream().cuda_stream
     assert lib.b200_maxpool3x3s2_fwd(x.data_ptr(), ptr("y"), ptr("arg"), n, c, h, w, cabi.BF16, st) == 0
-    assert lib.b200_maxpool3x3s2_bwd(dy.data_ptr(), ptr("arg"), ptr("dx"), n, c, h, w, cabi.BF16, st) == 0
+    assert lib.b200_maxpool3x3s2_bwd(dy.data_ptr(), None, ptr("arg"), ptr("dx"), n, c, h, w, cabi.BF16, st) == 0
     torch.cuda.synchronize()
     for k, (whole, pad) in bufs.items():
         assert _guards_intact(whole, pad, sizes[k]), k
