@@ -147,7 +147,10 @@ class SyntheticImageNet:
         else:
             self.images = img.to(dev)
         self._fixed = None
+        self._queue = None
         self.h2d_bytes = (img.numel() if host else 0) + batch_size * (16 + 1 + 8)
+        if host:
+            self._start_producer()   # the first epoch's crop parameters are being drawn while the caller sets up
 
     def __len__(self):
         return self.steps
@@ -175,9 +178,10 @@ class SyntheticImageNet:
             slot["target"] = target.to(dev, non_blocking=True)
             slot["ready"].record(self._stream)
 
-    def _param_stream(self):
-        """Per-step (boxes, flips, target) drawn by a helper thread a few steps ahead of the consumer, in
-        the same order a single thread would draw them (the generator is only touched by the helper)."""
+    def _start_producer(self):
+        """Helper thread that draws the per-step (boxes, flips, target) a few steps ahead of the consumer, in the same
+        order a single thread would draw them (the generator is only touched by the helper).  Like the workers of a
+        DataLoader it starts when the loader is built / an epoch ends, not at the first ``next()``."""
         import queue
         import threading
 
@@ -191,6 +195,12 @@ class SyntheticImageNet:
                 q.put(e)
 
         threading.Thread(target=work, daemon=True).start()
+        self._queue = q
+
+    def _param_stream(self):
+        if self._queue is None:
+            self._start_producer()
+        q, self._queue = self._queue, None
         for _ in range(self.steps):
             item = q.get()
             if isinstance(item, BaseException):
