@@ -46,6 +46,7 @@ def parse():
     ap.add_argument("--image", type=int, default=224)
     ap.add_argument("--src", type=int, default=256, help="synthetic source image size (uint8 HxWx3)")
     ap.add_argument("--fp32", action="store_true")
+    ap.add_argument("--bucket-mb", type=int, default=25, help="gradient bucket cap of the DDP wrapper (N>1), MiB")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-graph", action="store_true",
@@ -225,7 +226,8 @@ def run_ours(a):
     dtype = torch.float32 if a.fp32 else torch.bfloat16
 
     torch.manual_seed(0)
-    model = b200.FlatDDP(b200.build_model(a.arch, 1000, dev, dtype).cuda(), device_ids=[local], output_device=local)
+    model = b200.FlatDDP(b200.build_model(a.arch, 1000, dev, dtype).cuda(), device_ids=[local], output_device=local,
+                         bucket_cap_mb=a.bucket_mb)
     if os.environ.get("B200_WGRAD_STREAM", "1") == "0":
         model.module.use_wgrad_stream(False)
     crit = b200.CrossEntropyLoss().cuda()
@@ -470,7 +472,7 @@ def run_ours(a):
             "config": {"workload": workload_name(a), "arch": a.arch, "per_gpu_batch": a.batch,
                        "global_batch": a.batch * world, "image": a.image, "parallelism": f"dp{world}",
                        "l2": "not flushed: one step streams >10 GB of activations, far larger than the 126 MB L2",
-                       "wgrad_side_stream": overlapped, "cuda_graph_replay": graphed},
+                       "wgrad_side_stream": overlapped, "cuda_graph_replay": graphed, "bucket_cap_mb": a.bucket_mb},
             "e2e": e2e, "gpu_launches": launches, "clocks": clocks, "roofline": roof, "cpu_baseline": cpu,
             "kernels": kernels, "allreduce": allreduce, "final_loss": final_loss, "host_enqueue_ms_per_step": host_ms, "notes": notes,
         }
