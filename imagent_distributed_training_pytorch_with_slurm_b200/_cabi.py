@@ -44,6 +44,10 @@ SIGNATURES = {
     "b200_bn_fwd_train_dual": (_i32, [_vp] * 12 + [_sz, _i64, _i32, _f32, _f32, _i32, _vp]),
     "b200_bn_bwd_dual": (_i32, [_vp] * 16 + [_sz, _i64, _i32, _i32, _vp]),
     "b200_pack_grads": (_i32, [_c.POINTER(_vp), _c.POINTER(_i64), _c.POINTER(_i64), _i32, _vp, _f32, _i32, _vp]),
+    "b200_peer_pad_bytes": (_sz, []),
+    "b200_peer_exchange_sgd": (_i32, [_c.POINTER(_vp), _c.POINTER(_vp), _c.POINTER(_vp), _c.POINTER(_vp), _vp, _i32, _i32,
+                                      _i32, _i64, _i64, _f32, _f32, _f32, _f32, _i32, _i32, _vp]),
+    "b200_peer_wait": (_i32, [_vp, _i32, _i32, _vp]),
     "b200_input_workspace_bytes": (_sz, [_i64, _i32, _i32, _i32, _i32]),
     "b200_input_crop_resize_flip_norm": (_i32, [_vp, _vp, _vp, _vp, _vp, _sz, _i64, _i32, _i32, _i32, _i32,
                                                 _c.POINTER(_f32), _c.POINTER(_f32), _i32, _i32, _vp]),
@@ -466,6 +470,35 @@ def maxpool_bwd(dy, arg, in_shape, dy2=None):
     stats.end("maxpool_bwd", 1, s, dx.numel() * dx.element_size() + dy.numel() * (dy.element_size() + 1)
               + (dy2.numel() * dy2.element_size() if dy2 is not None else 0))
     return dx
+
+
+# ---- K4c ------------------------------------------------------------------------------------------
+def peer_pad_words():
+    return int(load().b200_peer_pad_bytes()) // 4
+
+
+def peer_table(ptrs):
+    """Host array of device pointers (one per rank) in the form the peer entry points take."""
+    return (_vp * len(ptrs))(*[int(p) for p in ptrs])
+
+
+def peer_exchange_sgd(grad_tab, param_tab, shadow_tab, pad_tab, momentum, rank, world, bucket, lo, hi, lr,
+                      weight_decay, momentum_coef, grad_scale, first_step, max_ctas=32):
+    _need_cuda(momentum)
+    s = stats.begin("peer_exchange")
+    _check(load().b200_peer_exchange_sgd(grad_tab, param_tab, shadow_tab, pad_tab, _ptr(momentum), rank, world, bucket,
+                                         lo, hi, lr, weight_decay, momentum_coef, grad_scale, int(bool(first_step)),
+                                         max_ctas, _stream()), "b200_peer_exchange_sgd")
+    # per rank: reads world gradient shards + p + buf, writes buf + world x (p + shadow)
+    n = (hi - lo) // world
+    stats.end("peer_exchange", 1, s, n * (4 * world + 8 + 4 + world * (4 + (2 if shadow_tab is not None else 0))))
+
+
+def peer_wait(pad, world, n_buckets):
+    _need_cuda(pad)
+    s = stats.begin("peer_wait")
+    _check(load().b200_peer_wait(_ptr(pad), world, n_buckets, _stream()), "b200_peer_wait")
+    stats.end("peer_wait", 1, s, 0)
 
 
 # ---- K1 -------------------------------------------------------------------------------------------

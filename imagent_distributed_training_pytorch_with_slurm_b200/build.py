@@ -13,7 +13,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libb200_imagenet.so")
-SOURCES = ["api.cu", "sgd.cu", "ce_topk.cu", "batchnorm.cu", "input.cu", "maxpool.cu", "pack.cu"]
+SOURCES = ["api.cu", "sgd.cu", "ce_topk.cu", "batchnorm.cu", "input.cu", "maxpool.cu", "pack.cu", "peer_exchange.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17", "--shared",
               "-Xcompiler", "-fPIC", "-cudart", "shared"]
 

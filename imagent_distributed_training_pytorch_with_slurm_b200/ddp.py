@@ -24,7 +24,7 @@ import torch.nn as nn
 
 class FlatDDP(nn.Module):
     def __init__(self, module, device_ids=None, output_device=None, process_group=None, bucket_cap_mb=25,
-                 first_bucket_mb=1, broadcast_buffers=True):
+                 first_bucket_mb=1, broadcast_buffers=True, exchange="nccl", optimizer=None, exchange_ctas=32):
         super().__init__()
         if not hasattr(module, "arena"):
             raise TypeError("FlatDDP wraps a B200ResNet (flat parameter arena); got " + type(module).__name__)
@@ -52,6 +52,60 @@ class FlatDDP(nn.Module):
             dist.broadcast(a.params, 0, group=process_group)
             dist.broadcast(module.buffer_arena, 0, group=process_group)
             a.refresh_shadow()
+        if exchange not in ("nccl", "peer"):
+            raise ValueError("exchange must be 'nccl' or 'peer'")
+        self.exchange = exchange if self.world_size > 1 else "nccl"
+        self.optimizer = optimizer
+        if self.exchange == "peer":
+            self._setup_peer(exchange_ctas)
+
+    # ---- opt-in: bucket exchange + SGD as one kernel over NVLink peer memory (K4c, csrc/peer_exchange.cu) ----
+    def _setup_peer(self, ctas):
+        import torch.distributed._symmetric_memory as symm_mem
+        from . import _cabi
+
+        a = self.module.arena
+        if not getattr(a, "symmetric", False):
+            raise TypeError("exchange='peer' needs build_model(..., symmetric=True): the arenas must be peer-mappable")
+        if self.world_size > 8 or len(self.buckets) > 24:
+            raise ValueError("exchange='peer' supports up to 8 ranks of one box and 24 buckets")
+        group = self.process_group if self.process_group is not None else dist.group.WORLD
+        self._peer_rank = dist.get_rank(group)
+        self._pad = symm_mem.empty(_cabi.peer_pad_words(), dtype=torch.int32, device=a.params.device).zero_()
+        handles = [symm_mem.rendezvous(t, group) for t in (a.grads, a.params, self._pad)]
+        hs = symm_mem.rendezvous(a.shadow, group) if a.shadow is not None else None
+        self._peer_handles = handles + [hs]   # keep the mappings alive
+        self._tab_grad = _cabi.peer_table(handles[0].buffer_ptrs)
+        self._tab_param = _cabi.peer_table(handles[1].buffer_ptrs)
+        self._tab_pad = _cabi.peer_table(handles[2].buffer_ptrs)
+        self._tab_shadow = _cabi.peer_table(hs.buffer_ptrs) if hs is not None else None
+        self._xstream = torch.cuda.Stream(device=a.params.device)
+        self._xctas = int(ctas)
+        torch.cuda.synchronize()
+        dist.barrier(group=group)          # every pad is zero before anyone raises a flag
+
+    def attach_optimizer(self, optimizer):
+        """exchange='peer' applies the optimizer's hyper-parameters inside the backward; FlatSGD.step() then only
+        advances the step count."""
+        self.optimizer = optimizer
+
+    def _peer_bucket(self, index, lo, hi):
+        from . import _cabi
+
+        if self.optimizer is None:
+            raise RuntimeError("exchange='peer' needs the optimizer: FlatDDP(..., optimizer=opt) or attach_optimizer(opt)")
+        g = self.optimizer.param_groups[0]
+        a = self.module.arena
+        main = torch.cuda.current_stream()
+        self._xstream.wait_stream(main)    # the gradients of this bucket are final in main-stream order
+        with torch.cuda.stream(self._xstream):
+            _cabi.peer_exchange_sgd(self._tab_grad, self._tab_param, self._tab_shadow, self._tab_pad, a.momentum,
+                                    self._peer_rank, self.world_size, index, lo, hi, float(g["lr"]),
+                                    float(g["weight_decay"]), float(g["momentum"]), 1.0, a.steps == 0, self._xctas)
+
+    def peer_error(self):
+        """True if a kernel of the peer exchange gave up waiting for another rank (call after a synchronise)."""
+        return self.exchange == "peer" and bool(self._pad[0].item() != 0)
 
     # ---- called by the model's backward ---------------------------------------------------------
     def wants(self, offset):
@@ -64,14 +118,24 @@ class FlatDDP(nn.Module):
         g = self.module.arena.grads
         while self._next < len(self.buckets) and self.buckets[self._next][0] >= offset:
             lo, hi = self.buckets[self._next]
-            self._works.append(dist.all_reduce(g[lo:hi], op=dist.ReduceOp.SUM, group=self.process_group,
-                                               async_op=True))
+            if self.exchange == "peer":
+                self._peer_bucket(self._next, lo, hi)
+            else:
+                self._works.append(dist.all_reduce(g[lo:hi], op=dist.ReduceOp.SUM, group=self.process_group,
+                                                   async_op=True))
             self._next += 1
 
     def backward_done(self):
         for w in self._works:
             w.wait()  # stream-level wait: the optimizer's kernels queue behind the all-reduces
         self._works = []
+        if self.exchange == "peer" and self._next > 0:
+            from . import _cabi
+
+            a = self.module.arena
+            torch.cuda.current_stream().wait_stream(self._xstream)
+            _cabi.peer_wait(self._pad, self.world_size, len(self.buckets))   # every shard of every rank has landed
+            a.applied_step = a.steps                                         # optimizer.step() only counts
         self._next = 0
         if self._buffer_work is not None:
             # the buffer broadcast had the whole backward to hide behind; joining it here (rather than at the

@@ -40,6 +40,9 @@ class FlatSGD(Optimizer):
             raise ValueError("closures are not supported")
         g = self.param_groups[0]
         a = self.arena
+        if a.applied_step == a.steps:   # FlatDDP(exchange="peer") updated every shard inside the backward
+            a.steps += 1
+            return None
         _cabi.sgd_flat(a.params, a.grads, a.momentum, a.shadow, float(g["lr"]), float(g["weight_decay"]),
                        float(g["momentum"]), 1.0, a.steps == 0)
         a.steps += 1

@@ -37,7 +37,7 @@ _conv_bwd = torch.ops.aten.convolution_backward.default
 class ParamArena:
     """Flat storage for parameters / gradients / momentum (float32) and the bf16 shadow."""
 
-    def __init__(self, shapes, device, shadow):
+    def __init__(self, shapes, device, shadow, symmetric=False):
         self.offsets = []
         off = 0
         for shp in shapes:
@@ -47,11 +47,23 @@ class ParamArena:
         self.numel = off
         self.shapes = list(shapes)
         self.device = device
-        self.params = torch.zeros(off, dtype=torch.float32, device=device)
-        self.grads = torch.zeros(off, dtype=torch.float32, device=device)
+        # symmetric=True: parameters, gradients and shadow come from torch's symmetric-memory allocator, so that the
+        # ranks of one box can map each other's arenas (FlatDDP(exchange="peer")); momentum stays private.
+        self.symmetric = bool(symmetric)
+        if symmetric:
+            import torch.distributed._symmetric_memory as symm_mem
+
+            def zeros(n, dtype):
+                return symm_mem.empty(n, dtype=dtype, device=device).zero_()
+        else:
+            def zeros(n, dtype):
+                return torch.zeros(n, dtype=dtype, device=device)
+        self.params = zeros(off, torch.float32)
+        self.grads = zeros(off, torch.float32)
         self.momentum = torch.zeros(off, dtype=torch.float32, device=device)
-        self.shadow = torch.zeros(off, dtype=torch.bfloat16, device=device) if shadow else None
+        self.shadow = zeros(off, torch.bfloat16) if shadow else None
         self.steps = 0
+        self.applied_step = -1   # FlatDDP(exchange="peer") sets this to `steps` when the update ran inside the backward
 
     def view(self, flat, i):
         shp = self.shapes[i]
@@ -300,7 +312,8 @@ class _WholeNet(torch.autograd.Function):
 class B200ResNet(nn.Module):
     """Drop-in for a torchvision ResNet (``models.<arch>(weights=None, num_classes=...)``)."""
 
-    def __init__(self, arch="resnet18", num_classes=1000, device=None, dtype=torch.bfloat16, wgrad_stream=True):
+    def __init__(self, arch="resnet18", num_classes=1000, device=None, dtype=torch.bfloat16, wgrad_stream=True,
+                 symmetric=False):
         super().__init__()
         import torchvision.models as tvm
 
@@ -325,6 +338,7 @@ class B200ResNet(nn.Module):
         for li in range(1, 5):
             setattr(self, f"layer{li}", nn.Sequential(*[_Block(b) for b in getattr(tv, f"layer{li}")]))
         self.fc = _Linear(tv.fc)
+        self._symmetric = bool(symmetric)   # read by _adopt when it allocates the arenas
         self._adopt(tv)
         if wgrad_stream and device.type == "cuda":
             self.use_wgrad_stream(True)
@@ -342,7 +356,7 @@ class B200ResNet(nn.Module):
         tv_mods = dict(tv.named_modules())
         names = [n for n, _ in tv.named_parameters()]
         self.arena = ParamArena([tuple(tv_params[n].shape) for n in names], self.device,
-                                shadow=self.act_dtype == torch.bfloat16)
+                                shadow=self.act_dtype == torch.bfloat16, symmetric=self._symmetric)
         a = self.arena
         self.param_names = names
         self.param_index = {n: i for i, n in enumerate(names)}
@@ -523,7 +537,8 @@ class B200ResNet(nn.Module):
             sink.backward_done()
 
 
-def build_model(arch="resnet18", num_classes=1000, device=None, dtype=torch.bfloat16):
+def build_model(arch="resnet18", num_classes=1000, device=None, dtype=torch.bfloat16, symmetric=False):
     """``models.resnet18(pretrained=False, num_classes=num_classes).cuda()`` (imagenet.py:312) with
-    ``arch`` generalised; call after ``torch.manual_seed`` like the reference does."""
-    return B200ResNet(arch, num_classes, device, dtype)
+    ``arch`` generalised; call after ``torch.manual_seed`` like the reference does.  ``symmetric=True`` places the
+    arenas in peer-mappable memory (needed by ``FlatDDP(exchange="peer")``)."""
+    return B200ResNet(arch, num_classes, device, dtype, symmetric=symmetric)

@@ -239,6 +239,32 @@ int b200_maxpool3x3s2_bwd(const void *dy, const void *dy2, const uint8_t *argmax
                           int w, int dtype, void *stream);
 
 /* ------------------------------------------------------------------------------------------------
+ * K4c  gradient exchange + optimizer step of one gradient bucket in ONE kernel over NVLink peer memory
+ * (opt-in: FlatDDP(exchange="peer"); the default path is NCCL all-reduce + b200_sgd_flat_f32).
+ * Replaces, per bucket, DDP's all-reduce (reducer.hpp:497-524, driven by loss.backward(), imagenet.py:128)
+ * followed by optimizer.step() (imagenet.py:131): every rank owns 1/world of the bucket, sums the world gradient
+ * shards in rank order through peer-mapped pointers (reduce-scatter), applies the update of b200_sgd_flat_f32, and
+ * writes the new parameters (+ bf16 shadow) into every rank's arena (all-gather).
+ *   grad_ptrs/param_ptrs/shadow_ptrs/pad_ptrs : HOST arrays of `world` DEVICE pointers, entry r = rank r's float32
+ *       gradient arena / float32 parameter arena / bf16 shadow (shadow_ptrs may be NULL) / signal pad, all mapped into
+ *       this process (cudaIpc / symmetric memory); entry `rank` is the local one.
+ *   momentum : this rank's float32 momentum arena (only the owned shard is read and written).
+ *   bucket   : 0..23, the same on every rank for the same [lo,hi) (element offsets, multiples of 4).
+ *   max_ctas : CTAs the kernel may use (it runs beside the backward); <= 0 means 32.
+ * Signal pads: b200_peer_pad_bytes() bytes per rank, zero before the first call, never touched by the host afterwards
+ * except word 0, which a kernel sets to 1 if a peer's flag did not arrive within ~20 s (the kernel then carries on
+ * instead of hanging the GPU; results of that step are garbage).  Every rank must launch the same buckets in the same
+ * order each iteration and finish the iteration with b200_peer_wait, which waits until every rank's shard of every
+ * bucket has arrived (and every peer has finished reading this rank's gradients) and advances the iteration counter.
+ */
+size_t b200_peer_pad_bytes(void);
+int b200_peer_exchange_sgd(const void *const *grad_ptrs, void *const *param_ptrs, void *const *shadow_ptrs,
+                           void *const *pad_ptrs, float *momentum, int rank, int world, int bucket, int64_t lo,
+                           int64_t hi, float lr, float weight_decay, float momentum_coef, float grad_scale,
+                           int first_step, int max_ctas, void *stream);
+int b200_peer_wait(void *my_pad, int world, int n_buckets, void *stream);
+
+/* ------------------------------------------------------------------------------------------------
  * K5  gradient packing: many weight-gradient tensors -> their slots of one flat float32 buffer.
  * Replaces the per-parameter `bucket_view.copy_(grad)` / `mul_out(grad, 1/W)` of DDP's Reducer
  * (reducer.hpp:347-406,497-500; driven by loss.backward(), imagenet.py:128) with one launch per flush:

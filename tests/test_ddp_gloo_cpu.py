@@ -47,6 +47,11 @@ def _worker(rank, world, port, gold, q):
                "nbt": int(sd["module.bn1.num_batches_tracked"]),
                "bn_rv": sd["module.bn1.running_var"].tolist()}
         q.put(out)
+    except BaseException as e:  # the parent must hear about it: a silent worker death would leave it waiting
+        import traceback
+
+        q.put({"rank": rank, "error": "".join(traceback.format_exception(type(e), e, e.__traceback__))})
+        raise
     finally:
         dist.destroy_process_group()
 
@@ -58,10 +63,29 @@ def test_flatddp_two_ranks_match_stock_ddp_golden():
     procs = [ctx.Process(target=_worker, args=(r, 2, 29641, gold, q)) for r in range(2)]
     for p in procs:
         p.start()
-    outs = sorted([q.get(), q.get()], key=lambda o: o["rank"])
-    for p in procs:
-        p.join(60)
-        assert p.exitcode == 0
+    outs = []
+    try:
+        import time
+
+        deadline = time.time() + 600
+        while len(outs) < 2:
+            if not q.empty():
+                outs.append(q.get())
+                if "error" in outs[-1]:
+                    break                # the other rank is stuck in a collective: do not wait for it
+            elif time.time() > deadline or all(not p.is_alive() for p in procs):
+                break
+            else:
+                time.sleep(0.2)
+    finally:
+        for p in procs:
+            p.join(5)
+            if p.is_alive():
+                p.terminate()
+    errors = [o["error"] for o in outs if "error" in o]
+    assert not errors, errors[0]
+    assert len(outs) == 2, "a worker exited without reporting"
+    outs = sorted(outs, key=lambda o: o["rank"])
     r0, r1 = outs
     # epoch averages (mean over ranks of loss / prec, unweighted over iterations) == stock DDP run
     for a, b in zip(r0["epoch"], gold["epoch_avg"]):

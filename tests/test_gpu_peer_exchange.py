@@ -1,0 +1,34 @@
+"""The opt-in peer-memory gradient exchange (K4c: reduce-scatter + SGD + all-gather of a bucket in one kernel over
+NVLink, csrc/peer_exchange.cu) on two GPUs of one box; skipped with fewer.  Checker at kernel level: the closed form
+(sum over ranks in rank order, then the update of b200_sgd_flat_f32, pinned by tests/test_gpu_kernels.py); at model
+level: the default FlatDDP(exchange="nccl") path, itself pinned against stock DistributedDataParallel."""
+import json
+import os
+import subprocess
+import sys
+
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs")
+def test_two_gpu_peer_exchange_matches_closed_form_and_nccl_path():
+    env = dict(os.environ, PYTHONPATH=ROOT, B200_PEER_TIMING="0")
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr",
+           "127.0.0.1", "--master-port", "29593", os.path.join(ROOT, "tests", "peer_exchange_worker.py")]
+    r = subprocess.run(cmd, env=env, capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-4000:]
+    out = json.loads([l for l in r.stdout.splitlines() if l.startswith("{")][-1])
+    k = out["kernel"]
+    assert k["error_word"] == 0 and k["step_counter"] == 3          # no flag timed out; three iterations counted
+    assert k["replicas_identical"] and k["shadow_ok"]              # every rank holds the same bits, shadow = bf16(p)
+    assert k["max_err"] <= k["bound"], k                           # float32, FMA contraction only
+    m = out["model"]
+    assert not m["peer"]["error"] and m["peer"]["identical"] and m["nccl"]["identical"]
+    assert m["peer"]["steps"] == m["nccl"]["steps"] == 3
+    for a, b in zip(m["peer"]["epoch"], m["nccl"]["epoch"]):
+        assert a == pytest.approx(b, rel=2e-4, abs=1e-6)           # same losses: only the summation order differs
+    assert m["global_rel_weight_diff"] < 1e-5, m
