@@ -47,6 +47,10 @@ def parse():
     ap.add_argument("--src", type=int, default=256, help="synthetic source image size (uint8 HxWx3)")
     ap.add_argument("--fp32", action="store_true")
     ap.add_argument("--bucket-mb", type=int, default=25, help="gradient bucket cap of the DDP wrapper (N>1), MiB")
+    ap.add_argument("--exchange", default="nccl", choices=["nccl", "peer"],
+                    help="N>1 gradient path: NCCL all-reduce + fused SGD (default), or the opt-in peer-memory kernel "
+                         "(experiment: no per-iteration buffer broadcast, whole iteration in one CUDA graph)")
+    ap.add_argument("--exchange-ctas", type=int, default=32)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-graph", action="store_true",
@@ -226,13 +230,16 @@ def run_ours(a):
     dtype = torch.float32 if a.fp32 else torch.bfloat16
 
     torch.manual_seed(0)
-    model = b200.FlatDDP(b200.build_model(a.arch, 1000, dev, dtype).cuda(), device_ids=[local], output_device=local,
-                         bucket_cap_mb=a.bucket_mb)
+    peer = a.exchange == "peer" and world > 1
+    model = b200.FlatDDP(b200.build_model(a.arch, 1000, dev, dtype, symmetric=peer).cuda(), device_ids=[local],
+                         output_device=local, bucket_cap_mb=a.bucket_mb, exchange=a.exchange,
+                         broadcast_buffers=not peer, exchange_ctas=a.exchange_ctas)
     if os.environ.get("B200_WGRAD_STREAM", "1") == "0":
         model.module.use_wgrad_stream(False)
     crit = b200.CrossEntropyLoss().cuda()
     opt = b200.FlatSGD(model.parameters(), 0.1, momentum=0.9, weight_decay=1e-4)
     b200.adjust_learning_rate(0.1, opt, 0)
+    model.attach_optimizer(opt)
     model.train()
 
     # ---- device-resident inputs (value): everything the step reads is in HBM before timing -------
@@ -273,7 +280,7 @@ def run_ours(a):
     launches_per_step = _cabi.stats.launches
     seg_runner = None
     notes = []
-    if graphed and world > 1:
+    if graphed and world > 1 and not peer:
         # multi-process: a chain of CUDA graphs cut at the NCCL collectives (SegmentedGraphStep); the input
         # kernel is launched eagerly in front of it
         seg_runner = b200.SegmentedGraphStep(model, crit, opt)
@@ -297,7 +304,7 @@ def run_ours(a):
             graphed, seg_runner = False, None
             notes.append("CUDA-graph replay disabled (capture failed on some rank); eager enqueue")
         barrier()
-    if graphed and world == 1:
+    if graphed and (world == 1 or peer):
         # The whole step as ONE CUDA graph (same kernels, same streams): per-step boxes / flips / targets are
         # copied device-to-device into the static buffers the graph reads, then the graph is replayed.  The
         # measurement no longer depends on how fast this host's Python can enqueue ~600 launches per step.
@@ -314,7 +321,7 @@ def run_ours(a):
 
         try:
             graph = torch.cuda.CUDAGraph()
-            with torch.cuda.graph(graph):
+            with torch.cuda.graph(graph, capture_error_mode="thread_local" if peer else "global"):
                 static_loss = body()
             arena.steps -= 1
 
@@ -472,7 +479,7 @@ def run_ours(a):
             "config": {"workload": workload_name(a), "arch": a.arch, "per_gpu_batch": a.batch,
                        "global_batch": a.batch * world, "image": a.image, "parallelism": f"dp{world}",
                        "l2": "not flushed: one step streams >10 GB of activations, far larger than the 126 MB L2",
-                       "wgrad_side_stream": overlapped, "cuda_graph_replay": graphed, "bucket_cap_mb": a.bucket_mb},
+                       "wgrad_side_stream": overlapped, "cuda_graph_replay": graphed, "bucket_cap_mb": a.bucket_mb, "exchange": a.exchange},
             "e2e": e2e, "gpu_launches": launches, "clocks": clocks, "roofline": roof, "cpu_baseline": cpu,
             "kernels": kernels, "allreduce": allreduce, "final_loss": final_loss, "host_enqueue_ms_per_step": host_ms, "notes": notes,
         }

@@ -146,6 +146,9 @@ class GraphedStep:
         self.seen, self.graph, self.x, self.t, self.out3 = 0, None, None, None, None
         inner = getattr(model, "module", model)
         self.arena = getattr(inner, "arena", None)
+        # a process that also runs NCCL (FlatDDP(exchange="peer") keeps it for metrics) must not let NCCL's watchdog
+        # thread invalidate the capture: confine capture errors to this thread
+        self.capture_error_mode = "thread_local" if getattr(model, "exchange", "nccl") == "peer" else "global"
 
     def _eager(self, x, t):
         logits = self.model(x)
@@ -168,7 +171,7 @@ class GraphedStep:
             self.t.copy_(t)
             torch.cuda.synchronize()
             self.graph = torch.cuda.CUDAGraph()
-            with torch.cuda.graph(self.graph):
+            with torch.cuda.graph(self.graph, capture_error_mode=self.capture_error_mode):
                 self.out3 = self._eager(self.x, self.t)
             if self.arena is not None:
                 self.arena.steps -= 1  # capture ran the Python of one step without executing it

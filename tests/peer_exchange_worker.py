@@ -90,6 +90,30 @@ def model_level(rank, local, world):
     return out
 
 
+def graph_level(rank, local, world):
+    """8 iterations of ResNet-18 (bf16): NCCL path eager vs peer path as ONE CUDA graph per iteration (3 eager warm-up
+    iterations, capture, replays).  No buffer broadcast in either, so the two differ only in how gradients meet."""
+    batches = [(x.cuda(), t.cuda()) for x, t in train_cpu.synthetic_batches(rank, 8, 16, 64, 1000, seed=77)]
+    out = {}
+    for mode in ("nccl", "peer"):
+        torch.manual_seed(5)
+        net = b200.build_model("resnet18", dtype=torch.bfloat16, symmetric=(mode == "peer")).cuda()
+        m = b200.FlatDDP(net, device_ids=[local], bucket_cap_mb=8, first_bucket_mb=1, exchange=mode,
+                         broadcast_buffers=False)
+        o = b200.FlatSGD(m.parameters(), 0.002, momentum=0.9, weight_decay=1e-4)
+        m.attach_optimizer(o)
+        runner = b200.GraphedStep(m, b200.CrossEntropyLoss().cuda(), o) if mode == "peer" else False
+        r = b200.train(batches, m, runner.criterion if runner else b200.CrossEntropyLoss().cuda(), o, 0, world,
+                       sync_every=1, lag=1, graph=runner)
+        torch.cuda.synchronize()
+        sd = m.state_dict()
+        out[mode] = {"epoch": list(map(float, r[:3])), "steps": m.module.arena.steps,
+                     "w": float(sd["module.fc.weight"].double().norm()),
+                     "w1": float(sd["module.conv1.weight"].double().norm()),
+                     "captured": bool(runner and runner.graph is not None), "error": bool(m.peer_error())}
+    return out
+
+
 def timing(rank, world, dev, n=25557056):
     import torch.distributed._symmetric_memory as symm_mem
 
@@ -138,6 +162,8 @@ def main():
     out = {"kernel": kernel_level(rank, world, dev, n, buckets)}
     if os.environ.get("B200_PEER_MODEL", "1") == "1":
         out["model"] = model_level(rank, local, world)
+    if os.environ.get("B200_PEER_GRAPH", "1") == "1":
+        out["graph"] = graph_level(rank, local, world)
     if os.environ.get("B200_PEER_TIMING", "1") == "1":
         out["timing"] = timing(rank, world, dev)
     if rank == 0:

@@ -32,3 +32,8 @@ def test_two_gpu_peer_exchange_matches_closed_form_and_nccl_path():
     for a, b in zip(m["peer"]["epoch"], m["nccl"]["epoch"]):
         assert a == pytest.approx(b, rel=2e-4, abs=1e-6)           # same losses: only the summation order differs
     assert m["global_rel_weight_diff"] < 1e-4, m   # measured 1.5e-5: summation order + fused update
+    # the same exchange with the whole iteration captured as one CUDA graph (bf16 activations, 8 iterations)
+    g = out["graph"]
+    assert g["peer"]["captured"] and not g["peer"]["error"] and g["peer"]["steps"] == g["nccl"]["steps"] == 8
+    assert g["peer"]["epoch"][0] == pytest.approx(g["nccl"]["epoch"][0], rel=2e-3) and g["peer"]["epoch"][1:] == g["nccl"]["epoch"][1:]
+    assert g["peer"]["w"] == pytest.approx(g["nccl"]["w"], rel=1e-4) and g["peer"]["w1"] == pytest.approx(g["nccl"]["w1"], rel=1e-4)
