@@ -49,7 +49,7 @@ def parse():
     ap.add_argument("--bucket-mb", type=int, default=25, help="gradient bucket cap of the DDP wrapper (N>1), MiB")
     ap.add_argument("--exchange", default="nccl", choices=["nccl", "peer"],
                     help="N>1 gradient path: NCCL all-reduce + fused SGD (default), or the opt-in peer-memory kernel "
-                         "(experiment: no per-iteration buffer broadcast, whole iteration in one CUDA graph)")
+                         "(whole iteration in one CUDA graph)")
     ap.add_argument("--exchange-ctas", type=int, default=32)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
@@ -233,7 +233,7 @@ def run_ours(a):
     peer = a.exchange == "peer" and world > 1
     model = b200.FlatDDP(b200.build_model(a.arch, 1000, dev, dtype, symmetric=peer).cuda(), device_ids=[local],
                          output_device=local, bucket_cap_mb=a.bucket_mb, exchange=a.exchange,
-                         broadcast_buffers=not peer, exchange_ctas=a.exchange_ctas)
+                         exchange_ctas=a.exchange_ctas)
     if os.environ.get("B200_WGRAD_STREAM", "1") == "0":
         model.module.use_wgrad_stream(False)
     crit = b200.CrossEntropyLoss().cuda()

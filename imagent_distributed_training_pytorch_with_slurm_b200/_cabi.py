@@ -47,7 +47,8 @@ SIGNATURES = {
     "b200_peer_pad_bytes": (_sz, []),
     "b200_peer_exchange_sgd": (_i32, [_c.POINTER(_vp), _c.POINTER(_vp), _c.POINTER(_vp), _c.POINTER(_vp), _vp, _i32, _i32,
                                       _i32, _i64, _i64, _f32, _f32, _f32, _f32, _i32, _i32, _vp]),
-    "b200_peer_wait": (_i32, [_vp, _i32, _i32, _vp]),
+    "b200_peer_bcast": (_i32, [_c.POINTER(_vp), _c.POINTER(_vp), _i64, _i32, _i32, _i32, _vp]),
+    "b200_peer_wait": (_i32, [_vp, _i32, _i32, _i32, _i32, _vp]),
     "b200_input_workspace_bytes": (_sz, [_i64, _i32, _i32, _i32, _i32]),
     "b200_input_crop_resize_flip_norm": (_i32, [_vp, _vp, _vp, _vp, _vp, _sz, _i64, _i32, _i32, _i32, _i32,
                                                 _c.POINTER(_f32), _c.POINTER(_f32), _i32, _i32, _vp]),
@@ -494,10 +495,17 @@ def peer_exchange_sgd(grad_tab, param_tab, shadow_tab, pad_tab, momentum, rank, 
     stats.end("peer_exchange", 1, s, n * (4 * world + 8 + 4 + world * (4 + (2 if shadow_tab is not None else 0))))
 
 
-def peer_wait(pad, world, n_buckets):
+def peer_bcast(buf_tab, pad_tab, nbytes, rank, world, root=0):
+    s = stats.begin("peer_bcast")
+    _check(load().b200_peer_bcast(buf_tab, pad_tab, nbytes, rank, world, root, _stream()), "b200_peer_bcast")
+    stats.end("peer_bcast", 1, s, 0 if rank == root else 2 * nbytes)
+
+
+def peer_wait(pad, world, n_buckets, rank, bcast_readers_of_me=False):
     _need_cuda(pad)
     s = stats.begin("peer_wait")
-    _check(load().b200_peer_wait(_ptr(pad), world, n_buckets, _stream()), "b200_peer_wait")
+    _check(load().b200_peer_wait(_ptr(pad), world, n_buckets, rank, int(bool(bcast_readers_of_me)), _stream()),
+           "b200_peer_wait")
     stats.end("peer_wait", 1, s, 0)
 
 

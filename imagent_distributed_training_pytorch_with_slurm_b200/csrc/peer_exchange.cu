@@ -116,11 +116,48 @@ peer_exchange_sgd_kernel(const __grid_constant__ PeerPtrs P, float *__restrict__
     }
 }
 
+// Buffer broadcast (DDP's per-iteration _sync_buffers, distributed.py:1590-1591, 2214-2257): the root raises a flag,
+// every other rank copies the root's buffer arena through its peer mapping and reports back; the root's
+// b200_peer_wait waits for those reports before its next forward may touch the buffers.  Uses the flag slots of the
+// last bucket index, which gradient buckets therefore may not use.
+constexpr int kBcastSlot = kMaxBuckets - 1;
+
 __global__ void __launch_bounds__(kThreads)
-peer_wait_kernel(unsigned *mypad, int world, int nbuckets) {
+peer_bcast_kernel(const __grid_constant__ PeerPtrs P, const unsigned char *root_buf, unsigned char *my_buf,
+                  long long nbytes, int rank, int world, int root) {
+    unsigned *mypad = P.pad[rank];
+    const unsigned seq = mypad[kSlotStep] + 1u;
+    if (rank == root) {
+        if (blockIdx.x == 0 && threadIdx.x < world) st_release_sys(P.pad[threadIdx.x] + flag_slot(kBcastSlot, 0, root), seq);
+        return;
+    }
+    if (threadIdx.x == 0 && !wait_flag(mypad + flag_slot(kBcastSlot, 0, root), seq)) mypad[0] = 1u;
+    __syncthreads();
+    const long long n8 = nbytes >> 3;
+    const uint2 *src = reinterpret_cast<const uint2 *>(root_buf);
+    uint2 *dst = reinterpret_cast<uint2 *>(my_buf);
+    for (long long i = (long long)blockIdx.x * kThreads + threadIdx.x; i < n8; i += (long long)gridDim.x * kThreads)
+        dst[i] = __ldcg(src + i);
+    if (blockIdx.x == 0 && threadIdx.x < (nbytes & 7)) my_buf[(n8 << 3) + threadIdx.x] = root_buf[(n8 << 3) + threadIdx.x];
+    __threadfence_system();
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        unsigned *counter = mypad + kSlotCounter + kBcastSlot;
+        if (atomicAdd(counter, 1u) == gridDim.x - 1) {
+            *counter = 0u;
+            st_release_sys(P.pad[root] + flag_slot(kBcastSlot, 1, rank), seq);   // "rank has read the root's buffers"
+        }
+    }
+}
+
+__global__ void __launch_bounds__(kThreads)
+peer_wait_kernel(unsigned *mypad, int world, int nbuckets, int bcast_readers_of_me, int rank) {
     const unsigned seq = mypad[kSlotStep] + 1u;
     for (int i = threadIdx.x; i < world * nbuckets; i += kThreads)
         if (!wait_flag(mypad + flag_slot(i / world, 1, i % world), seq)) mypad[0] = 1u;
+    if (bcast_readers_of_me && threadIdx.x < world && threadIdx.x != rank &&
+        !wait_flag(mypad + flag_slot(kBcastSlot, 1, threadIdx.x), seq))
+        mypad[0] = 1u;
     __syncthreads();
     if (threadIdx.x == 0) mypad[kSlotStep] = seq;   // the next iteration's flags use seq + 1
 }
@@ -134,8 +171,8 @@ extern "C" int b200_peer_exchange_sgd(const void *const *grad_ptrs, void *const 
                                       int64_t lo, int64_t hi, float lr, float weight_decay, float momentum_coef,
                                       float grad_scale, int first_step, int max_ctas, void *stream) {
     if (!grad_ptrs || !param_ptrs || !pad_ptrs || !momentum) return (int)cudaErrorInvalidValue;
-    if (world < 1 || world > kMaxRanks || rank < 0 || rank >= world || bucket < 0 || bucket >= kMaxBuckets)
-        return (int)cudaErrorInvalidValue;
+    if (world < 1 || world > kMaxRanks || rank < 0 || rank >= world || bucket < 0 || bucket >= kMaxBuckets - 1)
+        return (int)cudaErrorInvalidValue;   // the last bucket index carries the buffer broadcast's flags
     if (lo < 0 || hi < lo || (lo & 3) || (hi & 3)) return (int)cudaErrorInvalidValue;
     PeerPtrs P;
     for (int p = 0; p < kMaxRanks; ++p) {
@@ -163,12 +200,35 @@ extern "C" int b200_peer_exchange_sgd(const void *const *grad_ptrs, void *const 
     return 0;
 }
 
-extern "C" int b200_peer_wait(void *my_pad, int world, int n_buckets, void *stream) {
-    if (!my_pad || world < 1 || world > kMaxRanks || n_buckets < 1 || n_buckets > kMaxBuckets)
+extern "C" int b200_peer_bcast(void *const *buf_ptrs, void *const *pad_ptrs, int64_t nbytes, int rank, int world, int root,
+                               void *stream) {
+    if (!buf_ptrs || !pad_ptrs || nbytes < 0 || world < 1 || world > kMaxRanks || rank < 0 || rank >= world || root < 0 ||
+        root >= world)
+        return (int)cudaErrorInvalidValue;
+    PeerPtrs P;
+    for (int p = 0; p < kMaxRanks; ++p) {
+        P.grad[p] = nullptr; P.param[p] = nullptr; P.shadow[p] = nullptr;
+        P.pad[p] = p < world ? static_cast<unsigned *>(pad_ptrs[p]) : nullptr;
+        if (p < world && (!P.pad[p] || !buf_ptrs[p])) return (int)cudaErrorInvalidValue;
+        if (p < world && (b200_misaligned(P.pad[p], 4) || b200_misaligned(buf_ptrs[p], 8))) return (int)cudaErrorMisalignedAddress;
+    }
+    int64_t ctas = (nbytes / 8 + kThreads - 1) / kThreads;
+    if (ctas > 16) ctas = 16;
+    if (ctas < 1) ctas = 1;
+    peer_bcast_kernel<<<(unsigned)ctas, kThreads, 0, static_cast<cudaStream_t>(stream)>>>(
+        P, static_cast<const unsigned char *>(buf_ptrs[root]), static_cast<unsigned char *>(buf_ptrs[rank]), nbytes, rank,
+        world, root);
+    B200_CHECK_LAUNCH();
+    return 0;
+}
+
+extern "C" int b200_peer_wait(void *my_pad, int world, int n_buckets, int rank, int bcast_readers_of_me, void *stream) {
+    if (!my_pad || world < 1 || world > kMaxRanks || n_buckets < 1 || n_buckets > kMaxBuckets - 1 || rank < 0 ||
+        rank >= world)
         return (int)cudaErrorInvalidValue;
     if (b200_misaligned(my_pad, 4)) return (int)cudaErrorMisalignedAddress;
     peer_wait_kernel<<<1, kThreads, 0, static_cast<cudaStream_t>(stream)>>>(static_cast<unsigned *>(my_pad), world,
-                                                                            n_buckets);
+                                                                            n_buckets, bcast_readers_of_me, rank);
     B200_CHECK_LAUNCH();
     return 0;
 }

@@ -67,8 +67,8 @@ class FlatDDP(nn.Module):
         a = self.module.arena
         if not getattr(a, "symmetric", False):
             raise TypeError("exchange='peer' needs build_model(..., symmetric=True): the arenas must be peer-mappable")
-        if self.world_size > 8 or len(self.buckets) > 24:
-            raise ValueError("exchange='peer' supports up to 8 ranks of one box and 24 buckets")
+        if self.world_size > 8 or len(self.buckets) > 23:
+            raise ValueError("exchange='peer' supports up to 8 ranks of one box and 23 buckets")
         group = self.process_group if self.process_group is not None else dist.group.WORLD
         self._peer_rank = dist.get_rank(group)
         self._pad = symm_mem.empty(_cabi.peer_pad_words(), dtype=torch.int32, device=a.params.device).zero_()
@@ -79,6 +79,10 @@ class FlatDDP(nn.Module):
         self._tab_param = _cabi.peer_table(handles[1].buffer_ptrs)
         self._tab_pad = _cabi.peer_table(handles[2].buffer_ptrs)
         self._tab_shadow = _cabi.peer_table(hs.buffer_ptrs) if hs is not None else None
+        hb = symm_mem.rendezvous(self.module.buffer_arena, group)
+        self._peer_handles.append(hb)
+        self._tab_buf = _cabi.peer_table(hb.buffer_ptrs)
+        self._bcast_issued = False
         self._xstream = torch.cuda.Stream(device=a.params.device)
         self._xctas = int(ctas)
         torch.cuda.synchronize()
@@ -134,7 +138,10 @@ class FlatDDP(nn.Module):
 
             a = self.module.arena
             torch.cuda.current_stream().wait_stream(self._xstream)
-            _cabi.peer_wait(self._pad, self.world_size, len(self.buckets))   # every shard of every rank has landed
+            # every shard of every rank has landed; rank 0 also waits until its buffers have been read
+            _cabi.peer_wait(self._pad, self.world_size, len(self.buckets), self._peer_rank,
+                            self._bcast_issued and self._peer_rank == 0)
+            self._bcast_issued = False
             a.applied_step = a.steps                                         # optimizer.step() only counts
         self._next = 0
         if self._buffer_work is not None:
@@ -160,7 +167,19 @@ class FlatDDP(nn.Module):
             self._buffer_work = None
         out = self.module(*args, **kwargs)
         if (self.world_size > 1 and self.broadcast_buffers and self.module.training and torch.is_grad_enabled()):
-            self._buffer_work = dist.broadcast(self.module.buffer_arena, 0, group=self.process_group, async_op=True)
+            if self.exchange == "peer":
+                # the same broadcast as a peer copy (a kernel, so the iteration stays capturable); joined, like the
+                # bucket kernels, by backward_done
+                from . import _cabi
+
+                self._xstream.wait_stream(torch.cuda.current_stream())
+                with torch.cuda.stream(self._xstream):
+                    _cabi.peer_bcast(self._tab_buf, self._tab_pad, self.module.buffer_arena.numel(), self._peer_rank,
+                                     self.world_size, 0)
+                self._bcast_issued = True
+            else:
+                self._buffer_work = dist.broadcast(self.module.buffer_arena, 0, group=self.process_group,
+                                                   async_op=True)
         return out
 
     def state_dict(self, *args, **kwargs):

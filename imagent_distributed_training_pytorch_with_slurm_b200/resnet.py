@@ -365,7 +365,12 @@ class B200ResNet(nn.Module):
         # buffer arena: [running_mean/var float32 ... | num_batches_tracked int64 ...] in one byte buffer
         fbytes = 4 * 2 * nfeat
         fbytes = (fbytes + 15) // 16 * 16
-        self.buffer_arena = torch.zeros(fbytes + 8 * len(bn_mods), dtype=torch.uint8, device=self.device)
+        if self._symmetric:
+            import torch.distributed._symmetric_memory as symm_mem
+
+            self.buffer_arena = symm_mem.empty(fbytes + 8 * len(bn_mods), dtype=torch.uint8, device=self.device).zero_()
+        else:
+            self.buffer_arena = torch.zeros(fbytes + 8 * len(bn_mods), dtype=torch.uint8, device=self.device)
         fview = self.buffer_arena[:4 * 2 * nfeat].view(torch.float32)
         iview = self.buffer_arena[fbytes:].view(torch.int64)
         own = dict(self.named_modules())

@@ -249,7 +249,7 @@ int b200_maxpool3x3s2_bwd(const void *dy, const void *dy2, const uint8_t *argmax
  *       gradient arena / float32 parameter arena / bf16 shadow (shadow_ptrs may be NULL) / signal pad, all mapped into
  *       this process (cudaIpc / symmetric memory); entry `rank` is the local one.
  *   momentum : this rank's float32 momentum arena (only the owned shard is read and written).
- *   bucket   : 0..23, the same on every rank for the same [lo,hi) (element offsets, multiples of 4).
+ *   bucket   : 0..22, the same on every rank for the same [lo,hi) (element offsets, multiples of 4).
  *   max_ctas : CTAs the kernel may use (it runs beside the backward); <= 0 means 32.
  * Signal pads: b200_peer_pad_bytes() bytes per rank, zero before the first call, never touched by the host afterwards
  * except word 0, which a kernel sets to 1 if a peer's flag did not arrive within ~20 s (the kernel then carries on
@@ -262,7 +262,13 @@ int b200_peer_exchange_sgd(const void *const *grad_ptrs, void *const *param_ptrs
                            void *const *pad_ptrs, float *momentum, int rank, int world, int bucket, int64_t lo,
                            int64_t hi, float lr, float weight_decay, float momentum_coef, float grad_scale,
                            int first_step, int max_ctas, void *stream);
-int b200_peer_wait(void *my_pad, int world, int n_buckets, void *stream);
+/* b200_peer_bcast: DDP's per-iteration buffer broadcast (distributed.py:1590-1591) in the same style - every rank but
+ * `root` copies the root's buffer arena (buf_ptrs: host array of `world` peer-mapped device pointers, nbytes each)
+ * into its own after the root's flag, and reports back; the ROOT passes bcast_readers_of_me = 1 to b200_peer_wait
+ * so that it does not touch its buffers again before everyone has read them.  Gradient buckets use indices 0..22. */
+int b200_peer_bcast(void *const *buf_ptrs, void *const *pad_ptrs, int64_t nbytes, int rank, int world, int root,
+                    void *stream);
+int b200_peer_wait(void *my_pad, int world, int n_buckets, int rank, int bcast_readers_of_me, void *stream);
 
 /* ------------------------------------------------------------------------------------------------
  * K5  gradient packing: many weight-gradient tensors -> their slots of one flat float32 buffer.

@@ -44,7 +44,7 @@ def kernel_level(rank, world, dev, n, buckets, steps=3, lr=0.05, wd=1e-4, mu=0.9
         for b, (lo, hi) in enumerate(buckets):
             _cabi.peer_exchange_sgd(tabs[0], tabs[1], tabs[2], tabs[3], mom, rank, world, b, lo, hi, lr, wd, mu, 1.0,
                                     s == 0, 16)
-        _cabi.peer_wait(pad, world, len(buckets))
+        _cabi.peer_wait(pad, world, len(buckets), rank)
         tot = torch.zeros(n)
         for r in range(world):
             tot = tot + grads_all[s][r]
@@ -90,16 +90,22 @@ def model_level(rank, local, world):
     return out
 
 
+def _same_on_all_ranks(t):
+    lo_t, hi_t = t.clone().float(), t.clone().float()
+    dist.all_reduce(lo_t, op=dist.ReduceOp.MIN)
+    dist.all_reduce(hi_t, op=dist.ReduceOp.MAX)
+    return bool(torch.equal(lo_t, hi_t))
+
+
 def graph_level(rank, local, world):
     """8 iterations of ResNet-18 (bf16): NCCL path eager vs peer path as ONE CUDA graph per iteration (3 eager warm-up
-    iterations, capture, replays).  No buffer broadcast in either, so the two differ only in how gradients meet."""
+    iterations, capture, replays), both with the per-iteration buffer broadcast from rank 0 (NCCL / peer copy)."""
     batches = [(x.cuda(), t.cuda()) for x, t in train_cpu.synthetic_batches(rank, 8, 16, 64, 1000, seed=77)]
     out = {}
     for mode in ("nccl", "peer"):
         torch.manual_seed(5)
         net = b200.build_model("resnet18", dtype=torch.bfloat16, symmetric=(mode == "peer")).cuda()
-        m = b200.FlatDDP(net, device_ids=[local], bucket_cap_mb=8, first_bucket_mb=1, exchange=mode,
-                         broadcast_buffers=False)
+        m = b200.FlatDDP(net, device_ids=[local], bucket_cap_mb=8, first_bucket_mb=1, exchange=mode)
         o = b200.FlatSGD(m.parameters(), 0.002, momentum=0.9, weight_decay=1e-4)
         m.attach_optimizer(o)
         runner = b200.GraphedStep(m, b200.CrossEntropyLoss().cuda(), o) if mode == "peer" else False
@@ -110,6 +116,8 @@ def graph_level(rank, local, world):
         out[mode] = {"epoch": list(map(float, r[:3])), "steps": m.module.arena.steps,
                      "w": float(sd["module.fc.weight"].double().norm()),
                      "w1": float(sd["module.conv1.weight"].double().norm()),
+                     "rv": float(sd["module.bn1.running_var"].double().norm()),
+                     "rv_all": _same_on_all_ranks(sd["module.layer4.1.bn2.running_var"]),
                      "captured": bool(runner and runner.graph is not None), "error": bool(m.peer_error())}
     return out
 
@@ -130,7 +138,7 @@ def timing(rank, world, dev, n=25557056):
         def once():
             _cabi.peer_exchange_sgd(tabs[0], tabs[1], tabs[2], tabs[3], mom, rank, world, 0, 0, n, 0.0, 0.0, 0.9, 1.0,
                                     False, ctas)
-            _cabi.peer_wait(pad, world, 1)
+            _cabi.peer_wait(pad, world, 1, rank)
 
         for _ in range(3):
             once()

@@ -37,3 +37,6 @@ def test_two_gpu_peer_exchange_matches_closed_form_and_nccl_path():
     assert g["peer"]["captured"] and not g["peer"]["error"] and g["peer"]["steps"] == g["nccl"]["steps"] == 8
     assert g["peer"]["epoch"][0] == pytest.approx(g["nccl"]["epoch"][0], rel=2e-3) and g["peer"]["epoch"][1:] == g["nccl"]["epoch"][1:]
     assert g["peer"]["w"] == pytest.approx(g["nccl"]["w"], rel=1e-4) and g["peer"]["w1"] == pytest.approx(g["nccl"]["w1"], rel=1e-4)
+    # BatchNorm buffers: rank 0's running statistics reach every rank through the peer copy, as through NCCL
+    assert g["peer"]["rv"] == pytest.approx(g["nccl"]["rv"], rel=1e-3)
+    assert g["peer"]["rv_all"] and g["nccl"]["rv_all"]
