@@ -30,6 +30,7 @@ SIGNATURES = {
     "b200_ce_topk_workspace_bytes": (_sz, [_i64]),
     "b200_ce_topk_fwd": (_i32, [_vp, _vp, _vp, _vp, _vp, _sz, _i64, _i64, _i32, _vp]),
     "b200_ce_topk_fwd_static": (_i32, [_vp, _vp, _vp, _vp, _i64, _i64, _i32, _vp]),
+    "b200_target_rank": (_i32, [_vp, _vp, _vp, _i64, _i64, _i32, _vp]),
     "b200_ce_bwd": (_i32, [_vp, _vp, _vp, _vp, _f32, _vp, _i64, _i64, _i32, _vp]),
     "b200_bn_vec": (_i32, [_i32]),
     "b200_bn_workspace_bytes": (_sz, [_i64, _i32, _i32]),
@@ -253,6 +254,20 @@ def ce_topk_fwd_static(logits, target, out3, row_lse):
     _check(load().b200_ce_topk_fwd_static(_ptr(logits), _ptr(target), _ptr(out3), _ptr(row_lse), n, c,
                                           dtype_code(logits), _stream()), "b200_ce_topk_fwd_static")
     stats.launches += 1
+
+
+def target_rank(logits, target):
+    """int32[N]: how many classes rank ahead of each row's target (ties: the lower class index is ahead)."""
+    _need_cuda(logits, target)
+    assert logits.dim() == 2 and logits.is_contiguous() and target.dtype == torch.int64 and target.is_contiguous()
+    n, c = logits.shape
+    assert target.numel() == n
+    rank = torch.empty(n, dtype=torch.int32, device=logits.device)
+    s = stats.begin("target_rank")
+    _check(load().b200_target_rank(_ptr(logits), _ptr(target), _ptr(rank), n, c, dtype_code(logits), _stream()),
+           "b200_target_rank")
+    stats.end("target_rank", 1, s, n * c * logits.element_size() + 12 * n)
+    return rank
 
 
 def ce_bwd(logits, target, row_lse, grad_out=None, scale=1.0):

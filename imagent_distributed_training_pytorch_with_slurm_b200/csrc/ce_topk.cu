@@ -178,7 +178,60 @@ ce_bwd_kernel(const T *__restrict__ logits, const int64_t *__restrict__ target, 
     }
 }
 
+// rank of the target class per row (the count behind accuracy() for ANY k): one warp per row, same tie rule as above
+template <typename T>
+__global__ void __launch_bounds__(kWarpsPerBlock * 32)
+target_rank_kernel(const T *__restrict__ logits, const int64_t *__restrict__ target, int32_t *__restrict__ rank,
+                   int64_t n, int64_t c, bool vec_ok) {
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int64_t row = (int64_t)blockIdx.x * kWarpsPerBlock + warp;
+    if (row >= n) return;
+    const T *x = logits + row * c;
+    const int64_t t = target[row];
+    const bool t_ok = (t >= 0 && t < c);
+    const float xt = t_ok ? to_f<T>(x[t]) : NAN;
+    int ahead = 0;
+    constexpr int V = RowVec<T>::N;
+    int64_t done = 0;
+    if (vec_ok) {
+        const int64_t nv = c / V;
+        for (int64_t v = lane; v < nv; v += 32) {
+            float e[V];
+            RowVec<T>::load(x + v * V, e);
+#pragma unroll
+            for (int k = 0; k < V; ++k) ahead += (e[k] > xt) || (e[k] == xt && v * V + k < t);
+        }
+        done = nv * V;
+    }
+    for (int64_t j = done + lane; j < c; j += 32) {
+        const float e = to_f<T>(x[j]);
+        ahead += (e > xt) || (e == xt && j < t);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) ahead += __shfl_xor_sync(0xffffffffu, ahead, o);
+    if (lane == 0) rank[row] = t_ok ? ahead : (int32_t)c;   // an invalid target is never "in the top k"
+}
+
 }  // namespace
+
+extern "C" int b200_target_rank(const void *logits, const int64_t *target, int32_t *rank, int64_t n, int64_t c,
+                                int dtype, void *stream) {
+    if (!logits || !target || !rank || n <= 0 || c <= 0) return (int)cudaErrorInvalidValue;
+    if (dtype != B200_F32 && dtype != B200_BF16) return (int)cudaErrorInvalidValue;
+    if (b200_misaligned(logits)) return (int)cudaErrorMisalignedAddress;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const int blocks = (int)((n + kWarpsPerBlock - 1) / kWarpsPerBlock);
+    const size_t esz = dtype == B200_F32 ? 4 : 2;
+    const bool vec_ok = ((size_t)c * esz) % 16 == 0;
+    if (dtype == B200_F32)
+        target_rank_kernel<float><<<blocks, kWarpsPerBlock * 32, 0, st>>>(static_cast<const float *>(logits), target,
+                                                                           rank, n, c, vec_ok);
+    else
+        target_rank_kernel<__nv_bfloat16><<<blocks, kWarpsPerBlock * 32, 0, st>>>(
+            static_cast<const __nv_bfloat16 *>(logits), target, rank, n, c, vec_ok);
+    B200_CHECK_LAUNCH();
+    return 0;
+}
 
 extern "C" size_t b200_ce_topk_workspace_bytes(int64_t n) {
     if (n < 0) n = 0;

@@ -16,8 +16,12 @@
 //   B[bucket][src]  "src has finished its shard of this bucket"     written by src's last CTA into every rank's pad
 // b200_peer_wait (a one-CTA kernel at the end of the backward) waits for all B flags: after it every parameter of the
 // step has arrived and every peer has finished reading this rank's gradients, so the next iteration may start.
-// A flag that does not arrive within ~20 s sets the error word (pad[0]) and the kernel carries on instead of hanging
-// the GPU; the host checks the word after synchronising.
+// A flag that does not arrive within ~20 s latches the error word (pad[0]) instead of hanging the GPU.  From then on
+// this rank's kernels store NOTHING into any parameter, shadow or momentum arena and raise no completion flag, and
+// b200_peer_wait leaves the iteration counter where it was - so the peers time out in turn, latch their own error
+// word and stop updating too: replicas are left as they were before the failing iteration, never half-updated from
+// gradients that were not final.  The host reads the word wherever it synchronises (FlatDDP.peer_error(), checked by
+// train() at the end of an epoch).
 #include "common.cuh"
 
 namespace {
@@ -63,10 +67,18 @@ peer_exchange_sgd_kernel(const __grid_constant__ PeerPtrs P, float *__restrict__
                          int bucket, long long b4, long long e4, float lr, float weight_decay, float mu,
                          float grad_scale, int first_step) {
     unsigned *mypad = P.pad[rank];
+    __shared__ int failed;
+    if (threadIdx.x == 0) failed = (int)*reinterpret_cast<volatile unsigned *>(mypad);   // latched by an earlier kernel
+    __syncthreads();
+    if (failed) return;                           // no flags, no stores: the peers run into their own time-out
     const unsigned seq = mypad[kSlotStep] + 1u;   // only this rank's b200_peer_wait writes the counter, after this kernel
     if (blockIdx.x == 0 && threadIdx.x < world) st_release_sys(P.pad[threadIdx.x] + flag_slot(bucket, 0, rank), seq);
-    if (threadIdx.x < world && !wait_flag(mypad + flag_slot(bucket, 0, threadIdx.x), seq)) mypad[0] = 1u;
+    if (threadIdx.x < world && !wait_flag(mypad + flag_slot(bucket, 0, threadIdx.x), seq)) {
+        mypad[0] = 1u;
+        failed = 1;
+    }
     __syncthreads();
+    if (failed) return;                           // some peer's gradients are not known to be final: touch nothing
 
     const float4 *myp = reinterpret_cast<const float4 *>(P.param[rank]);
     float4 *mom = reinterpret_cast<float4 *>(momentum);
@@ -126,13 +138,21 @@ __global__ void __launch_bounds__(kThreads)
 peer_bcast_kernel(const __grid_constant__ PeerPtrs P, const unsigned char *root_buf, unsigned char *my_buf,
                   long long nbytes, int rank, int world, int root) {
     unsigned *mypad = P.pad[rank];
+    __shared__ int failed;
+    if (threadIdx.x == 0) failed = (int)*reinterpret_cast<volatile unsigned *>(mypad);
+    __syncthreads();
+    if (failed) return;
     const unsigned seq = mypad[kSlotStep] + 1u;
     if (rank == root) {
         if (blockIdx.x == 0 && threadIdx.x < world) st_release_sys(P.pad[threadIdx.x] + flag_slot(kBcastSlot, 0, root), seq);
         return;
     }
-    if (threadIdx.x == 0 && !wait_flag(mypad + flag_slot(kBcastSlot, 0, root), seq)) mypad[0] = 1u;
+    if (threadIdx.x == 0 && !wait_flag(mypad + flag_slot(kBcastSlot, 0, root), seq)) {
+        mypad[0] = 1u;
+        failed = 1;
+    }
     __syncthreads();
+    if (failed) return;                           // the root's statistics never arrived: keep this rank's own
     const long long n8 = nbytes >> 3;
     const uint2 *src = reinterpret_cast<const uint2 *>(root_buf);
     uint2 *dst = reinterpret_cast<uint2 *>(my_buf);
@@ -152,14 +172,23 @@ peer_bcast_kernel(const __grid_constant__ PeerPtrs P, const unsigned char *root_
 
 __global__ void __launch_bounds__(kThreads)
 peer_wait_kernel(unsigned *mypad, int world, int nbuckets, int bcast_readers_of_me, int rank) {
+    __shared__ int failed;
+    if (threadIdx.x == 0) failed = (int)*reinterpret_cast<volatile unsigned *>(mypad);
+    __syncthreads();
+    if (failed) return;                              // an exchange kernel of this iteration gave up: do not count it
     const unsigned seq = mypad[kSlotStep] + 1u;
     for (int i = threadIdx.x; i < world * nbuckets; i += kThreads)
-        if (!wait_flag(mypad + flag_slot(i / world, 1, i % world), seq)) mypad[0] = 1u;
+        if (!wait_flag(mypad + flag_slot(i / world, 1, i % world), seq)) {
+            mypad[0] = 1u;
+            failed = 1;
+        }
     if (bcast_readers_of_me && threadIdx.x < world && threadIdx.x != rank &&
-        !wait_flag(mypad + flag_slot(kBcastSlot, 1, threadIdx.x), seq))
+        !wait_flag(mypad + flag_slot(kBcastSlot, 1, threadIdx.x), seq)) {
         mypad[0] = 1u;
+        failed = 1;
+    }
     __syncthreads();
-    if (threadIdx.x == 0) mypad[kSlotStep] = seq;   // the next iteration's flags use seq + 1
+    if (threadIdx.x == 0 && !failed) mypad[kSlotStep] = seq;   // the next iteration's flags use seq + 1
 }
 
 }  // namespace

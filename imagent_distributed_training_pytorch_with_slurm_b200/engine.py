@@ -206,6 +206,10 @@ class SegmentedGraphStep:
 
         if not (isinstance(model, FlatDDP) and isinstance(criterion, CrossEntropyLoss) and isinstance(optimizer, FlatSGD)):
             raise TypeError("SegmentedGraphStep drives FlatDDP(B200ResNet) + CrossEntropyLoss + FlatSGD")
+        if getattr(model, "exchange", "nccl") != "nccl":
+            # the peer exchange keeps momentum sharded by rank and updates inside the backward; this runner records
+            # NCCL all-reduces + the flat SGD kernel over the whole arena - mixing the two corrupts the replicas
+            raise ValueError("SegmentedGraphStep is the NCCL path; FlatDDP(exchange='peer') runs as one GraphedStep")
         self.ddp, self.net, self.criterion, self.optimizer = model, model.module, criterion, optimizer
         self.eager = GraphedStep(model, criterion, optimizer)
         self.seen, self.plan, self.x, self.t, self.out3 = 0, None, None, None, None
@@ -318,6 +322,22 @@ def _to_device(t):
     return t if t.is_cuda else t.cuda(non_blocking=True)
 
 
+def _meter_weight(input):
+    """The reference weights every meter update with ``input[0].size(0)`` (imagenet.py:142,199), which is the
+    channel count of an NCHW image batch - 3 - not the batch size.  The space-to-depth stem layout of the input
+    kernel carries 16 channels per cell for the same RGB image, so the reference's number is stated here."""
+    return 3 if getattr(input, "_b200_s2d_stem", None) is not None else input[0].size(0)
+
+
+def _raise_on_exchange_error(model):
+    """FlatDDP(exchange="peer"): a rank that gave up waiting for a peer skips its updates and latches an error word;
+    surface it where the host is synchronised anyway (end of an epoch) instead of training on silently."""
+    check = getattr(model, "peer_error", None)
+    if check is not None and check():
+        raise RuntimeError("peer-memory gradient exchange timed out waiting for another rank; parameters were left "
+                           "untouched from the failing iteration on - restart from the last checkpoint")
+
+
 def train(train_loader, model, criterion, optimizer, epoch, world_size, sync_every=None, lag=0, graph=False):
     batch_time, data_time = AverageMeter(), AverageMeter()
     losses, top1, top5 = AverageMeter(), AverageMeter(), AverageMeter()
@@ -327,8 +347,10 @@ def train(train_loader, model, criterion, optimizer, epoch, world_size, sync_eve
     if graph:
         # one whole-iteration graph for a single process; with NCCL inside, the capture is invalidated on this
         # stack (torch 2.11, NCCL 2.28), so multi-process runs use a chain of graphs cut at the collectives
+        # (FlatDDP(exchange="peer") is nothing but kernel launches, so it is a single graph at any world size)
+        segmented = world_size > 1 and getattr(model, "exchange", "nccl") == "nccl"
         graphed = graph if isinstance(graph, (GraphedStep, SegmentedGraphStep)) else \
-            (SegmentedGraphStep if world_size > 1 else GraphedStep)(model, criterion, optimizer)
+            (SegmentedGraphStep if segmented else GraphedStep)(model, criterion, optimizer)
     start = end = time.time()
     for i, (input, target) in enumerate(train_loader):
         data_time.update(time.time() - end)
@@ -346,13 +368,14 @@ def train(train_loader, model, criterion, optimizer, epoch, world_size, sync_eve
             triple = _triple(criterion, loss, logits, target)
 
         iters += 1
-        if log.add(triple, input[0].size(0)):
+        if log.add(triple, _meter_weight(input)):
             if lag == 0:
                 torch.cuda.synchronize()  # imagenet.py:147
             batch_time.update(time.time() - end)
         end = time.time()
     log.finish()
     torch.cuda.synchronize()
+    _raise_on_exchange_error(model)
     total = time.time() - start
     if batch_time.count < iters:  # spread the un-attributed wall time evenly; the sum is what is reported
         rest = iters - batch_time.count
@@ -374,7 +397,7 @@ def validate(val_loader, model, criterion, world_size, sync_every=None, lag=0):
             logits = model(input)
             loss = criterion(logits, target)
             iters += 1
-            if log.add(_triple(criterion, loss, logits, target), input[0].size(0)):
+            if log.add(_triple(criterion, loss, logits, target), _meter_weight(input)):
                 if lag == 0:
                     torch.cuda.synchronize()
                 batch_time.update(time.time() - end)

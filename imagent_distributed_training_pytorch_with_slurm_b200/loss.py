@@ -11,8 +11,9 @@ import torch.nn as nn
 from . import _cabi
 
 # most recent (logits, target) pair and its result; holding the tensors keeps their memory from
-# being handed to another tensor, so a pointer match means "the same batch"
-_last = {"key": None, "out3": None, "hold": None}
+# being handed to another tensor, so a pointer match means "the same batch" - as long as nobody wrote into
+# them in place since, which their version counters tell (detach() shares the counter of the original)
+_last = {"key": None, "out3": None, "hold": None, "versions": None}
 
 
 def _key(logits, target):
@@ -20,7 +21,19 @@ def _key(logits, target):
 
 
 def _remember(logits, target, out3):
-    _last["key"], _last["out3"], _last["hold"] = _key(logits, target), out3, (logits.detach(), target)
+    hold = (logits.detach(), target.detach())
+    _last["key"], _last["out3"], _last["hold"] = _key(logits, target), out3, hold
+    _last["versions"] = (hold[0]._version, hold[1]._version)
+
+
+def _cached(logits, target):
+    """The remembered result if (logits, target) is the remembered pair and neither was modified in place."""
+    if _last["key"] != _key(logits, target):
+        return None
+    hold = _last["hold"]
+    if (hold[0]._version, hold[1]._version) != _last["versions"]:
+        return None
+    return _last["out3"]
 
 
 class _CEFn(torch.autograd.Function):
@@ -59,14 +72,23 @@ class CrossEntropyLoss(nn.Module):
 
 
 def accuracy(output, target, topk=(1,)):
-    """precision@k in percent as 1-element float32 tensors (imagenet.py:63-79); k in {1, 5}."""
-    for k in topk:
-        if k not in (1, 5):
-            raise NotImplementedError("the fused kernel reports top-1 and top-5 (what the reference logs)")
+    """precision@k in percent as 1-element float32 tensors, for any tuple of k (imagenet.py:63-79).
+
+    k = 1 and k = 5 (what the reference logs, imagenet.py:134) come out of the fused loss kernel; any other k is
+    counted from the rank of the target class (``b200_target_rank``): ``100/N * #{n : rank_n < k}``, which is what
+    ``topk(maxk) -> eq -> sum`` gives on tie-free logits."""
+    topk = tuple(int(k) for k in topk)
+    if any(k < 1 for k in topk):
+        raise ValueError("k must be >= 1")
     with torch.no_grad():
         output = output if output.is_contiguous() else output.contiguous()
-        if _last["key"] == _key(output, target):
-            out3 = _last["out3"]
-        else:
-            out3, _ = _cabi.ce_topk_fwd(output, target)
-        return [out3[1:2] if k == 1 else out3[2:3] for k in topk]
+        if max(topk) > output.size(1):
+            raise RuntimeError("selected index k out of range")      # what output.topk(maxk) raises in the reference
+        if all(k in (1, 5) for k in topk):
+            out3 = _cached(output, target)
+            if out3 is None:
+                out3, _ = _cabi.ce_topk_fwd(output, target)
+            return [out3[1:2] if k == 1 else out3[2:3] for k in topk]
+        rank = _cabi.target_rank(output, target)
+        pct = 100.0 / output.size(0)
+        return [(rank < k).sum().reshape(1).float().mul_(pct) for k in topk]

@@ -30,8 +30,10 @@ class FlatSGD(Optimizer):
             raise ValueError("FlatSGD must own every parameter of the arena")
 
     def zero_grad(self, set_to_none=True):
-        """No-op: every backward overwrites the whole gradient arena (the reference clears the grads
-        before each backward, imagenet.py:127, and never accumulates)."""
+        """Nothing to clear: every backward overwrites the whole gradient arena (the reference clears the grads
+        before each backward, imagenet.py:127, and never accumulates).  It re-arms the guard that makes a second
+        backward without ``zero_grad()``/``step()`` raise instead of silently replacing the first one's gradients."""
+        self.arena.grads_pending = False
         return None
 
     @torch.no_grad()
@@ -40,6 +42,7 @@ class FlatSGD(Optimizer):
             raise ValueError("closures are not supported")
         g = self.param_groups[0]
         a = self.arena
+        a.grads_pending = False
         if a.applied_step == a.steps:   # FlatDDP(exchange="peer") updated every shard inside the backward
             a.steps += 1
             return None

@@ -64,6 +64,9 @@ class ParamArena:
         self.shadow = zeros(off, torch.bfloat16) if shadow else None
         self.steps = 0
         self.applied_step = -1   # FlatDDP(exchange="peer") sets this to `steps` when the update ran inside the backward
+        # True between a backward and the next zero_grad()/step(): the backward OVERWRITES the gradient arena, so a
+        # second backward in that window would silently drop the first one's gradients where autograd accumulates
+        self.grads_pending = False
 
     def view(self, flat, i):
         shp = self.shapes[i]
@@ -344,6 +347,9 @@ class B200ResNet(nn.Module):
             self.use_wgrad_stream(True)
         self.__dict__["_stem_s2d"] = None
         self._anchor = torch.zeros((), device=device, requires_grad=True)
+        # load_state_dict (directly or through the data-parallel wrapper) writes the float32 arena only: bring the
+        # bf16 shadow and the rearranged stem weight, which is what the convolutions actually read, up to date
+        self.register_load_state_dict_post_hook(lambda module, incompatible: module.weights_changed())
         self.__dict__["_sink"] = None  # data-parallel wrapper (grad_ready / backward_done); not a submodule
         self.grad_predivide = 1.0  # 1/world_size, set by the wrapper (DDP's pre-division)
 
@@ -414,6 +420,13 @@ class B200ResNet(nn.Module):
             for bi, _ in enumerate(getattr(self, f"layer{li}")):
                 self._marks[(li, bi)] = a.offsets[self.param_index[f"layer{li}.{bi}.conv1.weight"]]
         self._marks["fc"] = a.offsets[self.param_index["fc.weight"]]
+
+    def weights_changed(self):
+        """Call after writing parameters other than through ``load_state_dict`` or the optimizer (e.g. an in-place
+        edit of ``p.data``): refreshes the bf16 shadow arena and drops the cached space-to-depth stem weight."""
+        self.arena.refresh_shadow()
+        if self._stem_s2d is not None:
+            self._stem_s2d._at = -1
 
     def mark_offsets(self):
         """Arena offsets (descending) at which gradients become final during the backward."""
@@ -501,7 +514,18 @@ class B200ResNet(nn.Module):
         feat = cur.mean((2, 3))
         return torch.addmm(self.fc.b_compute, feat, self.fc.w_compute.t())
 
+    def zero_grad(self, set_to_none=True):
+        """``p.grad`` is a permanent view of the gradient arena and every backward overwrites all of it, so there is
+        nothing to clear (and the views must not be dropped); this only re-arms the accumulation guard."""
+        self.arena.grads_pending = False
+
     def _backward(self, tape, g_logits):
+        if self.arena.grads_pending:
+            raise RuntimeError(
+                "backward() called twice without optimizer.zero_grad() or optimizer.step() in between: this model "
+                "writes gradients in place of the previous ones (the reference clears them before every backward, "
+                "imagenet.py:127) and does not accumulate")
+        self.arena.grads_pending = True
         sink = self._sink
         fc = self.fc
         g_logits = g_logits.contiguous()

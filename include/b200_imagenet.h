@@ -108,6 +108,13 @@ int b200_ce_topk_fwd(const void *logits, const int64_t *target, float *out3, flo
 int b200_ce_topk_fwd_static(const void *logits, const int64_t *target, float *out3, float *row_lse, int64_t n,
                             int64_t c, int dtype, void *stream);
 
+/* accuracy(output, target, topk) for ANY tuple of k (imagenet.py:63-79: output.topk(maxk, 1, True, True), eq, sum):
+ * rank[n] = #{j : x_nj > x_nt or (x_nj == x_nt and j < t)} as int32, so precision@k = 100/N * #{n : rank[n] < k} for
+ * every k from one pass (the reference's top-k select + transpose + eq per call).  Same tie rule as b200_ce_topk_fwd;
+ * a target outside [0, c) gets rank c.  No workspace. */
+int b200_target_rank(const void *logits, const int64_t *target, int32_t *rank, int64_t n, int64_t c, int dtype,
+                     void *stream);
+
 /* Backward of the loss above (loss.backward(), imagenet.py:128, first node):
  *     dlogits[n][j] = (exp(x_nj - row_lse[n]) - [j == t_n]) * scale * (grad_out ? *grad_out : 1) / N
  * grad_out is a DEVICE scalar (the upstream gradient, 1.0 for loss.backward()) or NULL; scale is a

@@ -96,6 +96,9 @@ def main():
     loss = torch.nn.CrossEntropyLoss()(logits, target)
     np.savez_compressed(os.path.join(OUT, "ce_topk_case.npz"), logits=logits.numpy(), target=target.numpy(),
                         loss=np.float32(loss.item()), prec1=np.float32(p1.item()), prec5=np.float32(p5.item()))
+    ks = (1, 2, 3, 5, 10, 50, 1000)                     # accuracy() accepts any tuple of k (imagenet.py:63-79)
+    g["accuracy_topk"] = {"case": "ce_topk_case.npz", "topk": list(ks),
+                          "prec": [float(v.item()) for v in ref.accuracy(logits, target, topk=ks)]}
     m = ref.AverageMeter()
     vals = [5.25, 4.5, 4.0, 3.125]
     for v in vals:

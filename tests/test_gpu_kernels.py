@@ -101,6 +101,41 @@ def test_ce_topk_golden_reference_accuracy():
     assert abs(out3[0] - c["loss"]) <= 2e-6 * c["loss"]
 
 
+def test_accuracy_for_any_topk_matches_reference_golden_and_oracle():
+    """accuracy() takes any tuple of k (imagenet.py:63-79); checked against the reference's own output on the golden
+    case (bit-exact) and against the oracle on bf16 logits, through the C ABI (b200_target_rank) and the wrapper."""
+    import json
+
+    from oracle import step_helpers as osh
+    import imagent_distributed_training_pytorch_with_slurm_b200 as b200
+
+    a = json.load(open(os.path.join(GOLD, "golden.json")))["accuracy_topk"]
+    c = np.load(os.path.join(GOLD, a["case"]))
+    x, t = torch.from_numpy(c["logits"]).to(DEV), torch.from_numpy(c["target"]).to(DEV)
+    got = b200.accuracy(x, t, topk=tuple(a["topk"]))
+    assert all(v.shape == (1,) and v.dtype == torch.float32 for v in got)
+    assert [v.item() for v in got] == a["prec"]
+    rank = cabi.target_rank(x, t).cpu().numpy()
+    assert np.array_equal(rank, osh.rank_of_target(c["logits"], c["target"]))
+    for n, cc, dtype in ((33, 1001, torch.bfloat16), (5, 4099, torch.float32), (256, 1000, torch.bfloat16)):
+        xb, tb = _ce_case(n, cc, 3 * n + cc, dtype)
+        ks = (1, 2, 7, 5, cc)
+        want = osh.accuracy_oracle(xb.float().numpy(), tb.numpy(), ks)
+        assert [v.item() for v in b200.accuracy(xb.to(DEV), tb.to(DEV), topk=ks)] == [float(w) for w in want]
+    with pytest.raises(RuntimeError):
+        b200.accuracy(x, t, topk=(1, 1001))                 # the reference's topk(maxk) raises here too
+    # the (1, 5) result cached by the criterion is dropped when the logits are modified in place afterwards
+    crit = b200.CrossEntropyLoss()
+    xb, tb = _ce_case(64, 1000, 9, torch.float32)
+    xb, tb = xb.to(DEV), tb.to(DEV)
+    crit(xb, tb)
+    before = [v.item() for v in b200.accuracy(xb, tb, topk=(1, 5))]
+    xb.neg_()
+    after = [v.item() for v in b200.accuracy(xb, tb, topk=(1, 5))]
+    want = osh.accuracy_oracle(xb.cpu().numpy(), tb.cpu().numpy(), (1, 5))
+    assert after == [float(w) for w in want] and after != before
+
+
 def test_ce_topk_ties_and_determinism():
     # all-equal rows: the target ranks behind the classes with a lower index
     x = torch.zeros(6, 16, device=DEV)

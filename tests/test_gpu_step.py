@@ -224,3 +224,33 @@ def test_graphed_training_matches_eager_training():
     assert sa == sb == 10
     assert a[0] == pytest.approx(b[0], rel=1e-3) and a[1] == b[1] and a[2] == b[2]
     assert torch.allclose(ya, yb, rtol=5e-2, atol=5e-2)
+
+
+def test_checkpoint_round_trip_into_a_bf16_model_evaluates_on_the_loaded_weights():
+    """The reference saves ``model.state_dict()`` (imagenet.py:388-392).  Loading that file back into a fresh bf16
+    model - bare or wrapped - must make the convolutions use the LOADED weights: they read a bf16 shadow arena and
+    a rearranged stem weight, which load_state_dict does not write itself."""
+    batches = train_cpu.synthetic_batches(0, 2, 8, 64, 1000)
+    trained, _, _ = _run_ours("resnet18", batches, torch.bfloat16, 0.05, 2)
+    sd = b200.FlatDDP(trained).state_dict()                     # 'module.'-prefixed float32, as the CLI writes it
+    loader = b200.SyntheticImageNet(8, 1, src_size=96, out_size=64, random_crop=False, seed=11)
+    x = next(iter(loader))[0]                                    # space-to-depth stem layout: exercises that cache too
+    trained.eval()
+    with torch.no_grad():
+        want = trained(x).float()
+    torch.manual_seed(123)                                       # a different random init
+    fresh = b200.FlatDDP(b200.build_model("resnet18", dtype=torch.bfloat16).cuda())
+    fresh.eval()
+    with torch.no_grad():
+        before = fresh(x).float()                                # also fills the stem-weight cache with the old weights
+    fresh.load_state_dict(sd)
+    with torch.no_grad():
+        got = fresh(x).float()
+    tol = 1e-2 * want.abs().max().item()   # same weights, same kernels; slack only for cuDNN picking another algorithm
+    assert torch.allclose(got, want, rtol=0, atol=tol) and not torch.allclose(before, want, rtol=0, atol=10 * tol)
+    # bare model, keys without the prefix
+    bare = b200.build_model("resnet18", dtype=torch.bfloat16).cuda().eval()
+    bare.load_state_dict({k[len("module."):]: v for k, v in sd.items()})
+    with torch.no_grad():
+        assert torch.allclose(bare(x).float(), want, rtol=0, atol=tol)
+    assert torch.equal(bare.arena.shadow, bare.arena.params.to(torch.bfloat16))
