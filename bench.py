@@ -22,6 +22,14 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
 METRIC = "ResNet-50 train images/sec"
+# BASELINE.json "configs" / BASELINE.md section 4 as one flag each (what the flag sets, what it is)
+CONFIGS = {
+    "A": ({"impl": "reference", "arch": "resnet18"}, "ResNet-18 DDP world_size 2 on CPU/gloo"),
+    "B": ({"arch": "resnet18", "batch": 256}, "ResNet-18 bf16 batch 256 on 1 GPU"),
+    "C": ({"arch": "resnet50", "batch": 256}, "ResNet-50 bf16 batch 256/GPU (headline; 1/2/4/8 GPUs)"),
+    "D": ({"arch": "resnet101", "batch": 256}, "ResNet-101 bf16 batch 256/GPU (2/4/8 GPUs)"),
+    "E": ({"arch": "resnet50", "batch": 1024}, "ResNet-50 bf16 channels-last batch 1024/GPU (8 GPUs)"),
+}
 
 
 def metric_name(a):
@@ -34,8 +42,12 @@ def metric_name(a):
 def parse():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=20)
-    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--steps", type=int, default=None, help="timed steps (default: 100 ours, BASELINE.md section 4; 10 for "
+                                                            "the CPU reference arm, 20 for --impl eager)")
+    ap.add_argument("--warmup", type=int, default=None, help="untimed warm-up steps (default 20 / 3 / 5)")
+    ap.add_argument("--config", default=None, choices=list(CONFIGS),
+                    help="BASELINE.json configuration preset: " + "; ".join(f"{k} = {v[1]}" for k, v in CONFIGS.items())
+                         + " (GPU count comes from the launch: --gpus N under torch.distributed.run)")
     ap.add_argument("--impl", default="ours", choices=["ours", "reference", "eager"],
                     help="ours | reference (the reference's step on the host cores) | eager (stock PyTorch on the GPU: "
                          "torchvision model + DDP + nn.CrossEntropyLoss + torch.optim.SGD, the incumbent)")
@@ -55,8 +67,19 @@ def parse():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-graph", action="store_true",
                     help="by default the step is replayed as CUDA graph(s) (host-independent); this keeps it eager")
-    ap.add_argument("--ref-batch", type=int, default=16, help="bounded CPU sample: images per reference step")
-    return ap.parse_args()
+    ap.add_argument("--ref-batch", type=int, default=32, help="bounded CPU sample: images per rank per reference step "
+                                                              "(SURVEY 8d: 32/rank, 2 gloo ranks)")
+    ap.add_argument("--no-incumbent", action="store_true", help="skip the stock-PyTorch-eager arms on the same GPU(s)")
+    ap.add_argument("--incumbent-steps", type=int, default=20)
+    ap.add_argument("--no-parity", action="store_true", help="N>1: skip the FlatDDP-vs-stock-DDP parity leg")
+    a = ap.parse_args()
+    if a.config:
+        for k, v in CONFIGS[a.config][0].items():
+            setattr(a, k, v)
+    d_steps, d_warm = {"ours": (100, 20), "reference": (10, 3), "eager": (20, 5)}[a.impl]
+    a.steps = d_steps if a.steps is None else a.steps
+    a.warmup = d_warm if a.warmup is None else a.warmup
+    return a
 
 
 def workload_name(a):
@@ -126,45 +149,59 @@ def traffic_per_launch(family):
 
 
 # ------------------------------------------------------------------------------------------------
+def _reference_ddp(arch, a, steps, warmup):
+    """north_star's CPU baseline: the reference's step restated for CPU
+    (oracle/train_cpu.py) driving stock DistributedDataParallel(torchvision model) + nn.CrossEntropyLoss + SGD on
+    TWO gloo ranks with cores//2 threads each, fp32 NCHW, ``--ref-batch`` images per rank."""
+    from oracle import train_cpu
+
+    return train_cpu.time_reference_ddp(arch, a.ref_batch, a.image, steps, warmup, world_size=2)
+
+
 def run_reference(a):
-    """The reference's own step (imagenet.py:97-151) restated for CPU (oracle/train_cpu.py), stock
-    torch modules, all host threads, on a bounded sample (``--ref-batch`` images per step)."""
+    """The reference's own data-parallel step (imagenet.py:97-151, --backend gloo) on the box's host cores.  It is a
+    HOST baseline: the same two gloo ranks whatever ``--gpus`` says, run and printed by rank 0 alone."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    from oracle import train_cpu
-
-    r = train_cpu.time_reference_step(a.arch, a.ref_batch, a.image, a.steps, a.warmup)
+    r = _reference_ddp(a.arch, a, a.steps, a.warmup)
+    second = None
+    if a.arch != "resnet18":   # BASELINE config A's network as a second figure
+        try:
+            r18 = _reference_ddp("resnet18", a, max(3, a.steps // 2), 2)
+            second = {"value": r18["images_per_sec"], "unit": "images/s", "sample": r18["sample"]}
+        except Exception as e:  # noqa: BLE001
+            second = {"error": f"{type(e).__name__}: {str(e)[:200]}"}
     v = r["images_per_sec"]
     print(json.dumps({
         "impl": "reference", "metric": metric_name(a), "value": v, "unit": "images/s", "n_gpus": a.gpus, "steps": a.steps,
         "warmup": a.warmup, "ms_per_step": r["ms_per_step"], "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": workload_name(a), "reference_arm": "CPU restatement of train() (oracle port), "
-                   "stock DDP-less single process, fp32 NCHW"},
+        "config": {"workload": workload_name(a),
+                   "reference_arm": "host baseline, identical at every --gpus N: CPU restatement of train() (oracle "
+                                    "port; the reference hard-codes .cuda()), stock DistributedDataParallel over gloo, "
+                                    f"world_size 2 x {r['threads_per_rank']} threads, fp32 NCHW, {a.ref_batch} "
+                                    "images/rank per step"},
         "cpu_baseline": {"value": v, "unit": "images/s", "cores": r["cores"], "kind": "port", "sample": r["sample"]},
+        "cpu_baseline_resnet18": second,
         "e2e": {"value": v, "unit": "images/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }))
 
 
-def run_eager(a):
-    """Stock PyTorch eager on the GPU, exactly the objects the reference builds (imagenet.py:312-325) driven by
-    its step order; reported for context only (the PyTorch-eager incumbent of SURVEY 8d)."""
+def _eager_measure(a, dev, rank, local, world, amp, steps, warmup):
+    """Stock PyTorch eager on the GPU: exactly the objects the reference builds (imagenet.py:312-325:
+    torchvision model, DistributedDataParallel when world > 1, nn.CrossEntropyLoss, torch.optim.SGD) driven in the
+    reference's step order (imagenet.py:119-134) on a resident float batch.  ``amp=False`` is the reference's own
+    configuration (fp32 NCHW); ``amp=True`` is the usual PyTorch fast path (bf16 autocast + channels_last).
+    Returns (images/s over all ranks, ms/step, final loss)."""
     import torch
     import torch.distributed as dist
     import torchvision
 
-    rank, local, world = (int(os.environ.get(k, d)) for k, d in (("RANK", "0"), ("LOCAL_RANK", "0"), ("WORLD_SIZE", "1")))
-    torch.cuda.set_device(local)
-    dev = torch.device("cuda", local)
-    if world > 1:
-        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-        dist.init_process_group("nccl", device_id=dev)
-    torch.backends.cudnn.benchmark = True
     torch.manual_seed(0)
     model = getattr(torchvision.models, a.arch)(weights=None, num_classes=1000).cuda()
-    if a.eager_amp:
+    if amp:
         model = model.to(memory_format=torch.channels_last)
     if world > 1:
         model = torch.nn.parallel.DistributedDataParallel(model, device_ids=[local], output_device=local)
@@ -172,12 +209,12 @@ def run_eager(a):
     opt = torch.optim.SGD(model.parameters(), 0.1, momentum=0.9, weight_decay=1e-4)
     g = torch.Generator().manual_seed(1234 + rank)
     x = torch.randn(a.batch, 3, a.image, a.image, generator=g).to(dev)
-    if a.eager_amp:
+    if amp:
         x = x.contiguous(memory_format=torch.channels_last)
     t = torch.randint(0, 1000, (a.batch,), generator=g).to(dev)
 
     def step():
-        with torch.autocast("cuda", dtype=torch.bfloat16, enabled=a.eager_amp):
+        with torch.autocast("cuda", dtype=torch.bfloat16, enabled=amp):
             logits = model(x)
             loss = crit(logits, t)
         opt.zero_grad()
@@ -186,27 +223,132 @@ def run_eager(a):
         _, pred = logits.topk(5, 1, True, True)  # accuracy(), imagenet.py:63-79
         return loss
 
-    for _ in range(a.warmup):
+    for _ in range(warmup):
         step()
     torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
-    for _ in range(a.steps):
+    for _ in range(steps):
         loss = step()
     e1.record()
     torch.cuda.synchronize()
     ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
     if world > 1:
         dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    final = float(loss)
+    del model, opt, x, step
+    torch.cuda.empty_cache()
+    return a.batch * world * steps / (float(ms) / 1e3), float(ms) / steps, final
+
+
+def run_eager(a):
+    """--impl eager: one stock-PyTorch arm as its own JSON line (the same measurement is part of the default line
+    as ``incumbent``)."""
+    import torch
+    import torch.distributed as dist
+
+    rank, local, world = (int(os.environ.get(k, d)) for k, d in (("RANK", "0"), ("LOCAL_RANK", "0"), ("WORLD_SIZE", "1")))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+    torch.backends.cudnn.benchmark = True
+    v, ms, loss = _eager_measure(a, dev, rank, local, world, a.eager_amp, a.steps, a.warmup)
     if rank == 0:
-        print(json.dumps({"impl": "eager", "metric": metric_name(a), "value": a.batch * world * a.steps / (float(ms) / 1e3),
+        print(json.dumps({"impl": "eager", "metric": metric_name(a), "value": v,
                           "unit": "images/s", "n_gpus": world, "steps": a.steps, "warmup": a.warmup,
-                          "ms_per_step": float(ms) / a.steps, "higher_is_better": True, "scaling": "weak",
+                          "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
                           "dtype": "bf16 autocast, channels_last" if a.eager_amp else "f32 NCHW (as the reference)",
                           "data": "synthetic, resident float tensors (no input stage)",
-                          "config": {"workload": workload_name(a)}, "final_loss": float(loss)}))
+                          "config": {"workload": workload_name(a)}, "final_loss": loss}))
     if world > 1:
         dist.destroy_process_group()
+
+
+def ddp_parity(dev, rank, local, world):
+    """N > 1: does the data-parallel path compute what the reference's DistributedDataParallel computes?
+    (imagenet.py:316 -> rank-0 parameter broadcast, bucket all-reduce of gradients pre-divided by the world size,
+    per-iteration rank-0 BatchNorm-buffer broadcast; imagenet.py:137-139 metric means.)  Three fp32 ResNet-18
+    iterations on per-rank batches through FlatDDP + FlatSGD and through stock DDP + torch.optim.SGD; ranks are
+    seeded differently so rank 0's initial weights must win in both.  Returns a dict for the JSON line."""
+    import torch
+    import torch.distributed as dist
+    import torchvision
+
+    import imagent_distributed_training_pytorch_with_slurm_b200 as b200
+
+    saved = (torch.backends.cudnn.allow_tf32, torch.backends.cuda.matmul.allow_tf32, torch.backends.cudnn.benchmark)
+    torch.backends.cudnn.allow_tf32 = torch.backends.cuda.matmul.allow_tf32 = False
+    torch.backends.cudnn.benchmark = False
+    try:
+        g = torch.Generator().manual_seed(1234 + rank)
+        batches = [(torch.randn(16, 3, 64, 64, generator=g).to(dev), torch.randint(0, 1000, (16,), generator=g).to(dev))
+                   for _ in range(3)]
+        lr = 0.002   # small: at random init and tiny batches the first layers' gradients are large and chaotic
+
+        def run(model, crit, opt):
+            model.train()
+            losses = []
+            for x, t in batches:
+                loss = crit(model(x), t)
+                opt.zero_grad()
+                loss.backward()
+                opt.step()
+                r = loss.detach().float().clone()
+                dist.all_reduce(r)
+                losses.append(float(r) / world)           # reduce_tensor(), imagenet.py:82-87
+            return losses
+
+        torch.manual_seed(100 + rank)
+        ours = b200.FlatDDP(b200.build_model("resnet18", dtype=torch.float32).cuda(), device_ids=[local],
+                            bucket_cap_mb=8, first_bucket_mb=1)
+        lo = run(ours, b200.CrossEntropyLoss().cuda(), b200.FlatSGD(ours.parameters(), lr, momentum=0.9, weight_decay=1e-4))
+        torch.manual_seed(100 + rank)
+        ref = torch.nn.parallel.DistributedDataParallel(torchvision.models.resnet18(weights=None).cuda(),
+                                                        device_ids=[local], bucket_cap_mb=8)
+        ls = run(ref, torch.nn.CrossEntropyLoss().cuda(),
+                 torch.optim.SGD(ref.parameters(), lr, momentum=0.9, weight_decay=1e-4))
+        osd, rsd = ours.state_dict(), ref.state_dict()
+        num = den = 0.0
+        stats_equal = True
+        for k in rsd:
+            if rsd[k].is_floating_point():
+                num += float((osd[k].double() - rsd[k].double()).pow(2).sum())
+                den += float(rsd[k].double().pow(2).sum())
+            else:
+                stats_equal &= bool(torch.equal(osd[k], rsd[k]))          # num_batches_tracked
+        # every replica must hold rank 0's parameters AND rank 0's running statistics after the iterations
+        # (state_dict() joins the last buffer broadcast)
+        flat = torch.cat([v.flatten().float() for v in osd.values()])
+        mn, mx = flat.clone(), flat.clone()
+        dist.all_reduce(mn, op=dist.ReduceOp.MIN)
+        dist.all_reduce(mx, op=dist.ReduceOp.MAX)
+        bufs = torch.cat([v.flatten().float() for k, v in osd.items() if "running_" in k])
+        rbufs = torch.cat([v.flatten().float() for k, v in rsd.items() if "running_" in k])
+        # stock DDP broadcasts rank 0's statistics at the NEXT forward, so after the last iteration only rank 0's
+        # copy is "rank 0's": compare there
+        sr = ((bufs - rbufs).norm() / rbufs.norm()).reshape(1)
+        dist.broadcast(sr, 0)
+        stats_rel = float(sr)
+        rel = (num / den) ** 0.5
+        loss_rel = max(abs(a_ - b_) / abs(b_) for a_, b_ in zip(lo, ls))
+        res = {"what": "3 fp32 ResNet-18 iterations, FlatDDP+FlatSGD vs stock DistributedDataParallel+SGD over NCCL, "
+                       "ranks seeded differently", "world_size": world,
+               "replicas_identical": bool(torch.equal(mn, mx)), "global_rel_weight_diff": rel, "loss_rel": loss_rel,
+               "loss_ours": lo, "loss_stock": ls, "running_stats_rel_diff_vs_stock": stats_rel,
+               "running_stats_equal_rank0": bool(torch.equal(mn, mx)) and stats_equal and stats_rel < 1e-3,
+               "keys_equal": list(osd) == list(rsd), "buckets": len(ours.buckets),
+               "tolerance": "global_rel_weight_diff < 1e-3, loss_rel < 1e-3 (cuDNN/NCCL summation order)"}
+        res["ok"] = bool(res["replicas_identical"] and rel < 1e-3 and loss_rel < 1e-3 and res["keys_equal"]
+                         and res["running_stats_equal_rank0"])
+        del ours, ref
+        torch.cuda.empty_cache()
+        return res
+    finally:
+        torch.backends.cudnn.allow_tf32, torch.backends.cuda.matmul.allow_tf32, torch.backends.cudnn.benchmark = saved
 
 
 def run_ours(a):
@@ -228,6 +370,10 @@ def run_ours(a):
     if os.environ.get("B200_CUDNN_BENCH_LIMIT"):
         torch.backends.cudnn.benchmark_limit = int(os.environ["B200_CUDNN_BENCH_LIMIT"])
     dtype = torch.float32 if a.fp32 else torch.bfloat16
+
+    parity = None
+    if world > 1 and not a.no_parity:
+        parity = ddp_parity(dev, rank, local, world)      # before anything is timed; < 10 s
 
     torch.manual_seed(0)
     peer = a.exchange == "peer" and world > 1
@@ -278,7 +424,7 @@ def run_ours(a):
     _cabi.stats.reset()
     step(a.warmup)                       # one more eager step just to count our launches per step
     launches_per_step = _cabi.stats.launches
-    seg_runner = None
+    seg_runner = graph = static_loss = None
     notes = []
     if graphed and world > 1 and not peer:
         # multi-process: a chain of CUDA graphs cut at the NCCL collectives (SegmentedGraphStep); the input
@@ -415,7 +561,7 @@ def run_ours(a):
             notes.append(f"allreduce timing failed: {type(e).__name__}: {str(e)[:200]}")
 
     # ---- end to end through the public API with HOST buffers ------------------------------------
-    e2e = None
+    e2e = wl = tl = use_graph = None
     if not a.no_e2e:
       try:
         fixed = os.environ.get("B200_E2E_FIXED_PARAMS", "0") == "1"  # diagnostic: skip the per-step crop draws
@@ -442,14 +588,38 @@ def run_ours(a):
         e2e = None
     clocks = sampler.stop() if rank == 0 else None
 
+    # ---- the incumbent on the same GPU(s): stock PyTorch eager with the reference's objects, in the reference's
+    # own configuration (fp32 NCHW) and in PyTorch's usual fast configuration (bf16 autocast, channels_last) ------
+    incumbent = None
+    if not a.no_incumbent:
+        import gc
+
+        del step, eager_step
+        model = crit = opt = images = params = seg_runner = graph = static_loss = wl = tl = use_graph = None
+        gc.collect()
+        torch.cuda.empty_cache()
+        incumbent = {"what": "stock torchvision model (+ DistributedDataParallel over NCCL at N > 1) + "
+                             "nn.CrossEntropyLoss + torch.optim.SGD, the reference's step order, resident float "
+                             "inputs (no input stage), CUDA events, max over ranks", "steps": a.incumbent_steps}
+        for key, amp in (("fp32_nchw", False), ("bf16_channels_last", True)):
+            try:
+                v, ms_i, _ = _eager_measure(a, dev, rank, local, world, amp, a.incumbent_steps, 5)
+                incumbent[key] = {"value": v, "unit": "images/s", "ms_per_step": ms_i}
+            except Exception as e:  # noqa: BLE001
+                incumbent[key] = {"error": f"{type(e).__name__}: {str(e)[:200]}"}
+                torch.cuda.empty_cache()
+
     if rank == 0:
         peak, peak_src = measured_peaks()
         kernels = {}
         for name, d in fam.items():
             nbytes = d["bytes"] + (box_bytes * a.steps // total if name == "input" else 0)
+            n8d = d["bytes_8d"] + (box_bytes * a.steps // total if name == "input" else 0)
             kernels[name] = {"calls": d["calls"], "ms_per_step": d["ms"] / a.steps,
                              "algorithmic_GB_per_step": nbytes / a.steps / 1e9,
-                             "GBps": nbytes / 1e9 / (d["ms"] / 1e3) if d["ms"] > 0 else None}
+                             "GBps": nbytes / 1e9 / (d["ms"] / 1e3) if d["ms"] > 0 else None,
+                             "survey_8d_GB_per_step": n8d / a.steps / 1e9,
+                             "GBps_survey_8d": n8d / 1e9 / (d["ms"] / 1e3) if d["ms"] > 0 else None}
         hbm = {k: v for k, v in kernels.items() if k in ("bn_fwd", "bn_bwd", "sgd", "input", "maxpool_fwd",
                                                          "maxpool_bwd", "pack")}
         dom = max(hbm, key=lambda k: hbm[k]["ms_per_step"]) if hbm else None
@@ -457,17 +627,20 @@ def run_ours(a):
         if dom:
             ach = hbm[dom]["GBps"]
             roof = {"kernel": dom, "bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s",
-                    "frac": ach / peak if ach else None, "traffic": traffic_per_launch(dom),
+                    "frac": ach / peak if ach else None,
+                    "frac_survey_8d": hbm[dom]["GBps_survey_8d"] / peak if hbm[dom]["GBps_survey_8d"] else None,
+                    "byte_models": "frac: bytes the kernels must move given their fusions (residual fan-in read in "
+                                   "both passes, ReLU bitmask, dual downsample form); frac_survey_8d: SURVEY 8(d)'s "
+                                   "un-fused per-site model (5/6 E*s backward, 3/4 E*s forward)",
+                    "traffic": traffic_per_launch(dom),
                     "peak_source": peak_src, "launches_per_step": hbm[dom]["calls"] / a.steps,
                     "share_of_step": hbm[dom]["ms_per_step"] / (ms_serial / a.steps),
                     "measured_in": f"second timed region of {a.steps} steps, kernels bracketed by CUDA events, "
                                    f"weight-gradient side stream off ({ms_serial / a.steps:.2f} ms/step)"}
         cpu = None
         if world == 1 and not a.no_cpu_baseline:
-            from oracle import train_cpu
-
             try:
-                r = train_cpu.time_reference_step(a.arch, a.ref_batch, a.image, 6, 1)
+                r = _reference_ddp(a.arch, a, 6, 1)
                 cpu = {"value": r["images_per_sec"], "unit": "images/s", "cores": r["cores"], "kind": "port",
                        "sample": r["sample"]}
             except Exception as e:  # noqa: BLE001
@@ -479,13 +652,18 @@ def run_ours(a):
             "config": {"workload": workload_name(a), "arch": a.arch, "per_gpu_batch": a.batch,
                        "global_batch": a.batch * world, "image": a.image, "parallelism": f"dp{world}",
                        "l2": "not flushed: one step streams >10 GB of activations, far larger than the 126 MB L2",
+                       "inputs": "one resident uint8 image batch per rank, re-used every step with fresh per-step crop "
+                                 "boxes / flips / targets (SURVEY 8d); the e2e leg streams a new host batch every step",
                        "wgrad_side_stream": overlapped, "cuda_graph_replay": graphed, "bucket_cap_mb": a.bucket_mb, "exchange": a.exchange},
             "e2e": e2e, "gpu_launches": launches, "clocks": clocks, "roofline": roof, "cpu_baseline": cpu,
+            "incumbent": incumbent, "parity": parity,
             "kernels": kernels, "allreduce": allreduce, "final_loss": final_loss, "host_enqueue_ms_per_step": host_ms, "notes": notes,
         }
-        print(json.dumps(out))
+        print(json.dumps(out), flush=True)
     if world > 1:
         dist.destroy_process_group()
+    if parity is not None and not parity["ok"]:
+        sys.exit(3)     # the line above is the record; a data-parallel path that disagrees with stock DDP is a failure
 
 
 if __name__ == "__main__":

@@ -134,7 +134,7 @@ class _Stats:
     def __init__(self):
         self.launches = 0
         self.timed = None  # set of family names or None
-        self.records = []  # (family, bytes, start_event, end_event)
+        self.records = []  # (family, bytes, start_event, end_event, bytes by SURVEY 8d's plain model)
 
     def reset(self):
         self.launches = 0
@@ -147,19 +147,23 @@ class _Stats:
             return e
         return None
 
-    def end(self, family, n_launch, start, nbytes):
+    def end(self, family, n_launch, start, nbytes, nbytes_8d=None):
+        """``nbytes``: what this call has to move given the fusions it implements; ``nbytes_8d``: the figure SURVEY
+        8(d)'s un-fused per-site model assigns to the same work (3/4 E*s forward, 5/6 E*s backward per BatchNorm site,
+        no mask, no fan-in), reported beside it."""
         self.launches += n_launch
         if start is not None:
             e = torch.cuda.Event(enable_timing=True)
             e.record()
-            self.records.append((family, nbytes, start, e))
+            self.records.append((family, nbytes, start, e, nbytes if nbytes_8d is None else nbytes_8d))
 
     def summary(self):
         out = {}
-        for fam, nbytes, s, e in self.records:
-            d = out.setdefault(fam, {"calls": 0, "bytes": 0, "ms": 0.0})
+        for fam, nbytes, s, e, n8d in self.records:
+            d = out.setdefault(fam, {"calls": 0, "bytes": 0, "ms": 0.0, "bytes_8d": 0})
             d["calls"] += 1
             d["bytes"] += nbytes
+            d["bytes_8d"] += n8d
             d["ms"] += s.elapsed_time(e)
         return out
 
@@ -320,7 +324,8 @@ def bn_fwd_train(x, z, gamma, beta, running_mean, running_var, num_batches_track
                                  _ptr(running_var), _ptr(num_batches_tracked), _ptr(saved), _ptr(ws), ws.numel(), m, c,
                                  eps, momentum, act, dt, _stream()), "b200_bn_fwd_train")
     e = m * c * x.element_size()
-    stats.end("bn_fwd", 3, s, (4 if act == ACT_ADD_RELU else 3) * e + (mask.numel() - 16 if mask is not None else 0))
+    stats.end("bn_fwd", 3, s, (4 if act == ACT_ADD_RELU else 3) * e + (mask.numel() - 16 if mask is not None else 0),
+              (4 if act == ACT_ADD_RELU else 3) * e)
     return y, saved, mask
 
 
@@ -370,7 +375,7 @@ def bn_bwd(dy, x, mask, gamma, saved, act, dgamma=None, dbeta=None, dy2=None):
     # algorithmic bytes: the two-pass model of SURVEY 8d; a second gradient branch is read in both passes
     # (+2E: it replaces the separate add kernel's 3E)
     stats.end("bn_bwd", 3, s, ((6 if act == ACT_ADD_RELU else 5) + (2 if dy2 is not None else 0)) * e
-              + (2 * (mask.numel() - 16) if mask is not None else 0))
+              + (2 * (mask.numel() - 16) if mask is not None else 0), (6 if act == ACT_ADD_RELU else 5) * e)
     return dx, dz, dgamma, dbeta
 
 
@@ -390,7 +395,7 @@ def bn_stats(x, gamma, beta, running_mean, running_var, num_batches_tracked, eps
     _check(lib.b200_bn_stats(_ptr(x), _ptr(gamma), _ptr(beta), _ptr(running_mean), _ptr(running_var),
                              _ptr(num_batches_tracked), _ptr(saved), _ptr(ws), ws.numel(), m, c, eps, momentum, dt,
                              _stream()), "b200_bn_stats")
-    stats.end("bn_fwd", 2, s, m * c * x.element_size())
+    stats.end("bn_fwd", 2, s, m * c * x.element_size(), 3 * m * c * x.element_size())   # 8d: a whole 'none' site
     return saved
 
 
@@ -413,7 +418,7 @@ def bn_fwd_train_dual(x, x2, saved2, gamma, beta, running_mean, running_var, num
                                     _ptr(running_var), _ptr(num_batches_tracked), _ptr(saved), _ptr(saved2), _ptr(ws),
                                     ws.numel(), m, c, eps, momentum, dt, _stream())
     _check(rc, "b200_bn_fwd_train_dual")
-    stats.end("bn_fwd", 3, s, 4 * m * c * x.element_size() + mask.numel() - 16)
+    stats.end("bn_fwd", 3, s, 4 * m * c * x.element_size() + mask.numel() - 16, 4 * m * c * x.element_size())
     return y, saved, mask
 
 
@@ -432,7 +437,7 @@ def bn_bwd_dual(dy, dy2, x, x2, mask, gamma, gamma2, saved, saved2, dgamma, dbet
                               _ptr(ws), ws.numel(), m, c, dt, _stream())
     _check(rc, "b200_bn_bwd_dual")
     e = m * c * x.element_size()
-    stats.end("bn_bwd", 3, s, (8 + (2 if dy2 is not None else 0)) * e + 2 * (mask.numel() - 16))
+    stats.end("bn_bwd", 3, s, (8 + (2 if dy2 is not None else 0)) * e + 2 * (mask.numel() - 16), 11 * e)  # 8d: 5E + 6E
     return dx, dx2
 
 

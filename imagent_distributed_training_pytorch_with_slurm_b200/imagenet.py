@@ -10,7 +10,8 @@ at ``epoch+1``), the best-epoch bookkeeping and the ``module.``-prefixed float32
 ``imagenet_FR_resnet18.pt`` (:388-392; ``imagenet_FR_<arch>.pt`` for other archs).
 
 Added flags default to the reference's behaviour where it has one: ``--arch resnet18``,
-``--image-size 448``.  ``--synthetic N`` (images per epoch) selects seeded synthetic uint8 data; the
+``--image-size 448``, float32 arithmetic (``--bf16`` selects the bf16 path), cuDNN autotuning off
+(``--cudnn-benchmark`` turns it on).  ``--synthetic N`` (images per epoch) selects seeded synthetic uint8 data; the
 on-disk ``datasets.ImageNet`` front end (imagenet.py:287-296) is outside this package's scope.
 Rendezvous: the reference's SLURM variables (:225-244) when present, else torchrun's
 ``RANK/LOCAL_RANK/WORLD_SIZE``, else a single process.
@@ -73,7 +74,8 @@ def run(args):
     print(prefix + "Hostname       : %s" % socket.gethostname())
 
     torch.cuda.set_device(local_rank)
-    torch.backends.cudnn.benchmark = True
+    if args.cudnn_benchmark:          # the reference leaves cuDNN's autotuner off (the PyTorch default)
+        torch.backends.cudnn.benchmark = True
     print("Initializing PyTorch distributed ...")
     dist.init_process_group(init_method="env://", backend=args.backend)
     print(f"Backend: {dist.get_backend()}")
@@ -87,7 +89,7 @@ def run(args):
     ref_mode = not args.random_crop
     mean, std = (b200_data.REFERENCE_MEAN, b200_data.REFERENCE_STD) if ref_mode else \
         (b200_data.IMAGENET_MEAN, b200_data.IMAGENET_STD)
-    dtype = torch.float32 if args.fp32 else torch.bfloat16
+    dtype = torch.bfloat16 if args.bf16 else torch.float32      # the reference trains in float32 (no autocast anywhere)
     per_rank = -(-args.synthetic // world_size)
     steps = -(-per_rank // args.batch_size)
     val_steps = max(1, steps // 25)
@@ -167,7 +169,13 @@ def build_parser():
     parser.add_argument("--random-crop", action="store_true", default=False,
                         help="RandomResizedCrop + horizontal flip + ImageNet mean/std instead of the reference's "
                              "plain resize and 0.5/0.5 normalisation")
-    parser.add_argument("--fp32", action="store_true", default=False, help="float32 activations instead of bf16")
+    parser.add_argument("--bf16", action="store_true", default=False,
+                        help="bf16 activations and bf16 tensor-core convolutions over float32 master weights (the fast "
+                             "path); default is float32 like the reference")
+    parser.add_argument("--fp32", action="store_true", default=False, help="float32 activations (the default; kept so "
+                                                                           "that older command lines still parse)")
+    parser.add_argument("--cudnn-benchmark", action="store_true", default=False,
+                        help="let cuDNN autotune its convolution algorithms (the reference does not)")
     return parser
 
 

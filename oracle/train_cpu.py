@@ -189,3 +189,52 @@ def time_reference_step(arch, batch, size, steps, warmup, num_classes=1000, lr=0
     dt = time.time() - t0
     return {"images_per_sec": batch * steps / dt, "ms_per_step": 1e3 * dt / steps, "cores": cores,
             "sample": f"{arch} fp32 NCHW batch {batch} at {size}x{size}, {steps} steps after {warmup} warm-up"}
+
+
+def _timed_ddp_worker(rank, world_size, port, arch, num_classes, lr, seed, batch, size, steps, warmup, threads, ret):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    torch.set_num_threads(threads)
+    dist.init_process_group("gloo", rank=rank, world_size=world_size)
+    try:
+        model, criterion, optimizer = build_reference_objects(arch, num_classes, lr, seed, world_size)
+        data = synthetic_batches(rank, 1, batch, size, num_classes)[0]
+        train_epoch_cpu([data] * warmup, model, criterion, optimizer, world_size)
+        dist.barrier()
+        t0 = time.time()
+        res = train_epoch_cpu([data] * steps, model, criterion, optimizer, world_size)
+        dist.barrier()
+        dt = time.time() - t0
+        if rank == 0:
+            ret.put({"seconds": dt, "loss_avg": float(res[0])})
+    finally:
+        dist.destroy_process_group()
+
+
+def time_reference_ddp(arch, batch_per_rank, size, steps, warmup, world_size=2, num_classes=1000, lr=0.1, seed=0,
+                       port=29633):
+    """Timed CPU baseline as SURVEY 8d / BASELINE.md 3 define it: the restated step on ``world_size`` gloo ranks
+    (the reference's ``--backend gloo`` data-parallel path, imagenet.py:316,440), ``cores // world_size`` threads per
+    rank, one fixed synthetic fp32 NCHW batch per rank, ``time.time()`` around the timed iterations with a barrier on
+    both sides.  Returns global images/sec with the core count."""
+    import torch.multiprocessing as mp
+
+    cores = len(os.sched_getaffinity(0))
+    threads = max(1, cores // world_size)
+    ctx = mp.get_context("spawn")
+    q = ctx.SimpleQueue()
+    procs = [ctx.Process(target=_timed_ddp_worker, args=(r, world_size, port, arch, num_classes, lr, seed, batch_per_rank,
+                                                         size, steps, warmup, threads, q))
+             for r in range(world_size)]
+    for p in procs:
+        p.start()
+    for p in procs:
+        p.join()
+    if any(p.exitcode != 0 for p in procs) or q.empty():
+        raise RuntimeError(f"gloo reference ranks failed (exit codes {[p.exitcode for p in procs]})")
+    out = q.get()
+    dt = out["seconds"]
+    return {"images_per_sec": batch_per_rank * world_size * steps / dt, "ms_per_step": 1e3 * dt / steps, "cores": cores,
+            "threads_per_rank": threads, "world_size": world_size, "loss_avg": out["loss_avg"],
+            "sample": f"{arch} fp32 NCHW, DDP over gloo world_size {world_size} x {threads} threads, batch "
+                      f"{batch_per_rank}/rank at {size}x{size}, {steps} steps after {warmup} warm-up"}

@@ -6,11 +6,17 @@ stall of cudaMalloc/cudaFree).  It must give exactly what the workspace-taking e
 runs the same kernel on a scratch array built into the library - on repeated calls, including when the
 batch size changes between calls (the array keeps stale contents from the previous call).
 
+Each call is checked twice: bit for bit against the workspace-taking entry point, and against the
+float64 oracle with the tolerances the other loss tests use.
+
 Collected last on purpose (file name), so a run that stops at the first failure has already executed
 every other test; it passes on its own in a fresh process as well.
 """
+import numpy as np
 import pytest
 import torch
+
+from oracle import cross_entropy as oce
 
 import imagent_distributed_training_pytorch_with_slurm_b200._cabi as cabi
 
@@ -41,6 +47,13 @@ def test_static_scratch_entry_matches_workspace_entry_on_consecutive_calls(dtype
         # tests is 2e-6 relative; this is stricter)
         assert torch.equal(out3, want3), (call, out3, want3)
         assert torch.equal(lse, want_lse)
+        # and directly against the oracle (float64 accumulation), with the tolerances of test_ce_topk_matches_oracle:
+        # loss 2e-6 relative, the two precision counts bit-exact, per-row log-sum-exp 2e-6
+        loss, t1, t5, _, row = oce.ce_topk_oracle(x.float().cpu().numpy(), t.cpu().numpy())
+        got = out3.cpu().numpy()
+        assert abs(got[0] - loss) <= 2e-6 * abs(loss)
+        assert got[1] == t1 and got[2] == t5
+        assert np.allclose(lse.cpu().numpy(), row, rtol=2e-6, atol=2e-6)
 
 
 def test_static_scratch_entry_rejects_batches_beyond_its_capacity():
