@@ -237,7 +237,7 @@ def _eager_measure(a, dev, rank, local, world, amp, steps, warmup):
     ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
     if world > 1:
         dist.all_reduce(ms, op=dist.ReduceOp.MAX)
-    final = float(loss)
+    final = float(loss.detach())
     del model, opt, x, step
     torch.cuda.empty_cache()
     return a.batch * world * steps / (float(ms) / 1e3), float(ms) / steps, final

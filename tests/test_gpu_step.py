@@ -3,7 +3,8 @@ committed golden trajectory.  -m gpu only.
 
 Tolerances: float32 activation mode - loss within 2e-3 relative, per-tensor gradient relative L2
 error <= 1e-2 (cuDNN vs CPU convolution order; ResNet-18 at random init amplifies ~1e-6 noise to
-~1e-4).  bf16 mode - loss within 3e-2 relative at step 1, gradient cosine >= 0.98 per large tensor.
+~1e-4).  bf16 mode - loss within 1e-2 relative at step 1, gradient errors held to what stock
+``torch.autocast(bfloat16)`` reaches on the same batch (see the bf16 test for the measured reason).
 """
 import json
 import os
@@ -90,26 +91,45 @@ def _stock_autocast_grads(arch, batch):
 
 
 def test_resnet18_bf16_step_within_bf16_tolerance():
-    """bf16 activations against the float32 oracle.  Tolerance: loss within 3e-2 relative; for every
-    large gradient tensor the angle to the oracle's gradient must be no worse than 1.5x (+0.01) what
-    stock PyTorch autocast-bf16 gets on the same batch (at random init a ResNet amplifies bf16
-    rounding enormously in the first layers, for any implementation)."""
-    batches = train_cpu.synthetic_batches(0, 1, 16, 64, 1000)
+    """bf16 activations against the float32 oracle, batch 64.
+
+    What a bf16 pipeline CAN reach was measured first (stock ``torch.autocast(bfloat16)`` against stock float32 on the
+    same batch, ResNet-18 at random init, batches 64-128, 64x64 to 224x224, also after 40 training steps): the loss
+    agrees to 5e-4, but per-tensor gradient relative L2 errors are 0.02 (fc) ... 0.17-0.27 (layer4) ... 0.39 (conv1),
+    i.e. cosine 0.92-0.999 - rounding to 8 bits is amplified by the cancellation in the weight-gradient sums of a
+    deep BatchNorm net.  SURVEY 8c's proposed "cosine >= 0.999 / rel-L2 <= 3e-2" is therefore out of reach for ANY
+    bf16 implementation, stock autocast included, and the yardstick has to be stock autocast itself:
+      * loss within 1e-2 relative of the oracle (SURVEY 8c);
+      * every gradient tensor >= 4096 elements: rel-L2 error <= 1.3 x stock autocast's on that tensor + 0.01
+        (where stock reaches 3e-2 this demands <= 5e-2; the old form allowed 0.14 there);
+      * all gradients concatenated: rel-L2 error <= 1.15 x stock autocast's.
+    A backward that is subtly wrong (a mask off by one channel, a missing 1/N, a stale statistic) fails the second and
+    third clause by a wide margin; the float32 step test above pins the same code path at 1e-2 per tensor."""
+    batches = train_cpu.synthetic_batches(0, 1, 64, 64, 1000)
     _, trace, grads = _run_ours("resnet18", batches, torch.bfloat16, 0.02, 1)
     res = train_cpu.run_ddp_oracle("resnet18", 1, [batches], lr=0.02, seed=0)
-    assert abs(trace[0][0] - res["trace"][0][0]) <= 3e-2 * abs(res["trace"][0][0])
+    assert abs(trace[0][0] - res["trace"][0][0]) <= 1e-2 * abs(res["trace"][0][0])
     og = _oracle_grads("resnet18", batches[0])
     sloss, sg = _stock_autocast_grads("resnet18", batches[0])
-    cos = torch.nn.functional.cosine_similarity
-    worst = 1.0
+
+    def rel(a, b):
+        return ((a - b).norm() / (b.norm() + 1e-30)).item()
+
+    rows = []
     for n, gr in grads.items():
         if gr.numel() < 4096:
             continue
-        ours = 1.0 - cos(gr.flatten(), og[n].flatten(), dim=0).item()
-        stock = 1.0 - cos(sg[n].flatten(), og[n].flatten(), dim=0).item()
-        assert ours <= 1.5 * stock + 0.01, (n, ours, stock)
-        worst = min(worst, 1.0 - ours)
-    assert worst > 0.8
+        ours, stock = rel(gr, og[n]), rel(sg[n], og[n])
+        rows.append((n, ours, stock))
+    cat = lambda d: torch.cat([d[n].flatten().double() for n in og])  # noqa: E731
+    g_ours, g_stock = rel(cat(grads), cat(og)), rel(cat(sg), cat(og))
+    out = os.path.join(os.path.dirname(GOLD), "..", "gpurun_out")
+    if os.path.isdir(out):
+        json.dump({"loss": [trace[0][0], float(res["trace"][0][0]), sloss], "global": [g_ours, g_stock],
+                   "per_tensor": rows}, open(os.path.join(out, "bf16_step_gradient_errors.json"), "w"))
+    for n, ours, stock in rows:
+        assert ours <= 1.3 * stock + 0.01, (n, ours, stock)
+    assert g_ours <= 1.15 * g_stock, (g_ours, g_stock)
 
 
 def test_resnet50_bf16_trains_and_loss_falls():
