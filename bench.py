@@ -315,6 +315,8 @@ def ddp_parity(dev, rank, local, world):
         num = den = 0.0
         stats_equal = True
         for k in rsd:
+            if "running_" in k:
+                continue                      # compared below, on rank 0 (stock ranks > 0 still hold their own)
             if rsd[k].is_floating_point():
                 num += float((osd[k].double() - rsd[k].double()).pow(2).sum())
                 den += float(rsd[k].double().pow(2).sum())
@@ -342,8 +344,10 @@ def ddp_parity(dev, rank, local, world):
                "running_stats_equal_rank0": bool(torch.equal(mn, mx)) and stats_equal and stats_rel < 1e-3,
                "keys_equal": list(osd) == list(rsd), "buckets": len(ours.buckets),
                "tolerance": "global_rel_weight_diff < 1e-3, loss_rel < 1e-3 (cuDNN/NCCL summation order)"}
-        res["ok"] = bool(res["replicas_identical"] and rel < 1e-3 and loss_rel < 1e-3 and res["keys_equal"]
-                         and res["running_stats_equal_rank0"])
+        ok = torch.tensor([1.0 if (res["replicas_identical"] and rel < 1e-3 and loss_rel < 1e-3 and res["keys_equal"]
+                                   and res["running_stats_equal_rank0"]) else 0.0], device=dev)
+        dist.all_reduce(ok, op=dist.ReduceOp.MIN)     # one verdict for the whole job
+        res["ok"] = bool(ok.item() == 1.0)
         del ours, ref
         torch.cuda.empty_cache()
         return res
@@ -661,6 +665,7 @@ def run_ours(a):
         }
         print(json.dumps(out), flush=True)
     if world > 1:
+        dist.barrier()                 # nobody leaves before rank 0 has printed the line
         dist.destroy_process_group()
     if parity is not None and not parity["ok"]:
         sys.exit(3)     # the line above is the record; a data-parallel path that disagrees with stock DDP is a failure

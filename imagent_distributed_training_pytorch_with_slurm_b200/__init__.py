@@ -14,6 +14,7 @@ accuracy                  accuracy                                 (loss.py)
 SGD                       FlatSGD / SGD                            (optim.py)
 DistributedSampler        DistributedSampler                       (sampler.py)
 transforms + DataLoader   DeviceInputStage, SyntheticImageNet      (data.py)
+datasets.ImageNet + DataLoader  ImageFolderIndex, ImageFolderLoader  (folder.py)
 train / validate / ...    engine.py (same names and signatures; GraphedStep / SegmentedGraphStep replay
                           an iteration as CUDA graph(s))
 run / CLI                 imagenet.py
@@ -22,6 +23,7 @@ from . import _cabi  # noqa: F401
 from ._cabi import B200Error  # noqa: F401
 from .data import DeviceInputStage, SyntheticImageNet, draw_batch_params, rrc_params  # noqa: F401
 from .ddp import DistributedDataParallel, FlatDDP  # noqa: F401
+from .folder import ImageFolderIndex, ImageFolderLoader  # noqa: F401
 from .engine import (AverageMeter, GraphedStep, SegmentedGraphStep, adjust_learning_rate, reduce_tensor, to_python_float, train,  # noqa: F401
                      validate)
 from .loss import CrossEntropyLoss, accuracy  # noqa: F401
@@ -31,5 +33,5 @@ from .sampler import DistributedSampler  # noqa: F401
 
 __all__ = ["B200Error", "B200ResNet", "ParamArena", "build_model", "FlatDDP", "DistributedDataParallel",
            "CrossEntropyLoss", "accuracy", "FlatSGD", "SGD", "DistributedSampler", "DeviceInputStage",
-           "SyntheticImageNet", "draw_batch_params", "rrc_params", "AverageMeter", "reduce_tensor",
+           "SyntheticImageNet", "ImageFolderIndex", "ImageFolderLoader", "draw_batch_params", "rrc_params", "AverageMeter", "reduce_tensor",
            "to_python_float", "adjust_learning_rate", "train", "validate", "GraphedStep", "SegmentedGraphStep"]

@@ -53,6 +53,9 @@ SIGNATURES = {
     "b200_input_workspace_bytes": (_sz, [_i64, _i32, _i32, _i32, _i32]),
     "b200_input_crop_resize_flip_norm": (_i32, [_vp, _vp, _vp, _vp, _vp, _sz, _i64, _i32, _i32, _i32, _i32,
                                                 _c.POINTER(_f32), _c.POINTER(_f32), _i32, _i32, _vp]),
+    "b200_input_crop_resize_flip_norm_ragged": (_i32, [_vp, _i64, _vp, _vp, _vp, _vp, _vp, _sz, _i64, _i32, _i32, _i32,
+                                                       _i32, _c.POINTER(_f32), _c.POINTER(_f32), _i32, _i32, _vp]),
+    "b200_interleave_planar_u8": (_i32, [_vp, _vp, _i64, _i64, _vp]),
 }
 
 _lib = None
@@ -566,3 +569,57 @@ def input_stage(images, boxes, flips, out_h, out_w, mean, std, out_dtype=torch.b
            "b200_input_crop_resize_flip_norm")
     stats.end("input", 2, s, n * 3 * out_h * out_w * out.element_size())  # + box bytes, added by the caller
     return out
+
+
+def _input_out(n, out_h, out_w, out_dtype, layout, device):
+    if layout == LAYOUT_NHWC:
+        return torch.empty((n, 3, out_h, out_w), dtype=out_dtype, device=device, memory_format=torch.channels_last)
+    if layout == LAYOUT_S2D_STEM:
+        if out_h % 2 or out_w % 2:
+            raise B200Error("the space-to-depth stem layout needs even output sizes")
+        out = torch.empty((n, 16, (out_h + 6) // 2, (out_w + 6) // 2), dtype=out_dtype, device=device,
+                          memory_format=torch.channels_last)
+        out._b200_s2d_stem = (out_h, out_w)
+        return out
+    return torch.empty((n, 3, out_h, out_w), dtype=out_dtype, device=device)
+
+
+def input_stage_ragged(slab, table, boxes, flips, max_h, max_w, out_h, out_w, mean, std, out_dtype=torch.bfloat16,
+                       layout=LAYOUT_NHWC):
+    """The input stage on a batch of images of different sizes: ``slab`` uint8 [bytes] (device) holds the interleaved
+    RGB images, ``table`` int64 [N,4] (device) = (byte offset, height, width, row pitch) per image, ``boxes`` int32
+    [N,4] each inside its image.  ``max_h`` / ``max_w`` bound the image sizes of the batch.  Output as ``input_stage``."""
+    _need_cuda(slab, table, boxes, flips)
+    n = table.shape[0]
+    assert slab.dtype == torch.uint8 and slab.dim() == 1 and slab.is_contiguous()
+    assert table.dtype == torch.int64 and table.shape == (n, 4) and table.is_contiguous()
+    assert boxes.dtype == torch.int32 and boxes.is_contiguous() and boxes.shape == (n, 4)
+    if flips is not None:
+        assert flips.dtype == torch.uint8 and flips.is_contiguous() and flips.numel() == n
+    lib = load()
+    out = _input_out(n, out_h, out_w, out_dtype, layout, slab.device)
+    nbytes = lib.b200_input_workspace_bytes(n, max_h, max_w, out_h, out_w)
+    if nbytes == 0:
+        raise B200Error("invalid input-stage geometry")
+    ws = workspace(slab.device, nbytes, "input")
+    mean3 = (_f32 * 3)(*[float(v) for v in mean])
+    std3 = (_f32 * 3)(*[float(v) for v in std])
+    s = stats.begin("input")
+    _check(lib.b200_input_crop_resize_flip_norm_ragged(_ptr(slab), slab.numel(), _ptr(table), _ptr(boxes), _ptr(flips),
+                                                       _ptr(out), _ptr(ws), ws.numel(), n, max_h, max_w, out_h, out_w,
+                                                       mean3, std3, F32 if out_dtype == torch.float32 else BF16, layout,
+                                                       _stream()), "b200_input_crop_resize_flip_norm_ragged")
+    stats.end("input", 2, s, n * 3 * out_h * out_w * out.element_size())
+    return out
+
+
+def interleave_planar(table, slab, max_pixels):
+    """Re-pack a batch of planar [3,h,w] uint8 images (what nvJPEG returns) into the interleaved ragged ``slab``;
+    ``table`` int64 [N,4] (device) = (address of the planar image, height, width, byte offset in the slab)."""
+    _need_cuda(table, slab)
+    assert table.dtype == torch.int64 and table.dim() == 2 and table.shape[1] == 4 and table.is_contiguous()
+    assert slab.dtype == torch.uint8 and slab.is_contiguous()
+    s = stats.begin("interleave")
+    _check(load().b200_interleave_planar_u8(_ptr(table), _ptr(slab), table.shape[0], int(max_pixels), _stream()),
+           "b200_interleave_planar_u8")
+    stats.end("interleave", 1, s, 0)

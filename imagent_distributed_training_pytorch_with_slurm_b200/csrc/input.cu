@@ -113,7 +113,7 @@ __global__ void __launch_bounds__(kThreads)
 input_resample_kernel(const uint8_t *__restrict__ images, const int32_t *__restrict__ boxes,
                       const uint8_t *__restrict__ flips, OutT *__restrict__ out, const int32_t *__restrict__ ws,
                       int src_h, int src_w, int out_h, int out_w, int KX, int KY, int max_src_rows, Norm nrm,
-                      int layout, int inter_bytes) {
+                      int layout, int inter_bytes, const int64_t *__restrict__ tab) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     float *lut = reinterpret_cast<float *>(smem_raw);          // [3][256]
     uint8_t *inter = smem_raw + 3 * 256 * sizeof(float);       // [max_src_rows][out_w][3]
@@ -152,7 +152,11 @@ input_resample_kernel(const uint8_t *__restrict__ images, const int32_t *__restr
 
         // horizontal pass: a thread owns an output column, keeps that column's taps in registers and
         // walks down the needed source rows -> 8-bit intermediate in shared memory
-        const uint8_t *img = images + ((int64_t)s * src_h + top + ylo) * (int64_t)src_w * 3 + (int64_t)left * 3;
+        // dense batch: sample s is image s of [n, src_h, src_w, 3]; ragged batch (tab != nullptr): sample s starts
+        // tab[4s] bytes into the slab and its rows are tab[4s+3] bytes apart
+        const int64_t pitch = tab ? tab[4 * s + 3] : (int64_t)src_w * 3;
+        const int64_t base = tab ? tab[4 * s] : (int64_t)s * src_h * pitch;
+        const uint8_t *img = images + base + (int64_t)(top + ylo) * pitch + (int64_t)left * 3;
         for (int xx = threadIdx.x; xx < out_w; xx += kThreads) {
             const int xmin = bx[2 * xx], cnt = bx[2 * xx + 1];
             const int32_t *k = cx + (int64_t)xx * KX;
@@ -161,7 +165,7 @@ input_resample_kernel(const uint8_t *__restrict__ images, const int32_t *__restr
             for (int t = 0; t < 8; ++t) kk[t] = (t < cnt) ? k[t] : 0;
             const uint8_t *px = img + xmin * 3;
             if (cnt <= 8) {
-                for (int rr = 0; rr < nrows; ++rr, px += (int64_t)src_w * 3) {
+                for (int rr = 0; rr < nrows; ++rr, px += pitch) {
                     int a0 = 1 << (kPrecisionBits - 1), a1 = a0, a2 = a0;
 #pragma unroll
                     for (int t = 0; t < 8; ++t) {
@@ -177,7 +181,7 @@ input_resample_kernel(const uint8_t *__restrict__ images, const int32_t *__restr
                     o[2] = (uint8_t)clip8(a2);
                 }
             } else {  // very strong down-scaling: taps stay in memory
-                for (int rr = 0; rr < nrows; ++rr, px += (int64_t)src_w * 3) {
+                for (int rr = 0; rr < nrows; ++rr, px += pitch) {
                     int a0 = 1 << (kPrecisionBits - 1), a1 = a0, a2 = a0;
                     for (int t = 0; t < cnt; ++t) {
                         const int kt = k[t];
@@ -289,7 +293,7 @@ __global__ void __launch_bounds__(kThreads, 5)
 input_s2d_kernel(const uint8_t *__restrict__ images, int64_t image_bytes, const int32_t *__restrict__ boxes,
                  const uint8_t *__restrict__ flips, OutT *__restrict__ out, const int32_t *__restrict__ ws,
                  const float *__restrict__ lut_g, int src_h, int src_w, int out_h, int out_w, int KX, int KY,
-                 int max_src_rows, int src_stride, int inter_stride) {
+                 int max_src_rows, int src_stride, int inter_stride, const int64_t *__restrict__ tab) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     float *lut = reinterpret_cast<float *>(smem_raw);                        // [3][256]
     uint32_t *src = reinterpret_cast<uint32_t *>(smem_raw + 3 * 256 * sizeof(float));  // [max_src_rows][src_stride]
@@ -318,8 +322,10 @@ input_s2d_kernel(const uint8_t *__restrict__ images, int64_t image_bytes, const 
         if (rows_ok) {
             // 1. stage the rows: 4 pixels = 12 bytes = (up to) 4 aligned words per step
             const int ngroups = (bw + 3) >> 2;
+            const int64_t pitch = tab ? tab[4 * s + 3] : (int64_t)src_w * 3;        // see input_resample_kernel
+            const int64_t base = tab ? tab[4 * s] : (int64_t)s * src_h * pitch;
             for (int rr = warp; rr < nrows; rr += kThreads / 32) {
-                const int64_t off = (((int64_t)s * src_h + top + ylo + rr) * src_w + left) * 3;
+                const int64_t off = base + (int64_t)(top + ylo + rr) * pitch + (int64_t)left * 3;
                 const uintptr_t addr = reinterpret_cast<uintptr_t>(images) + (uintptr_t)off;
                 const unsigned sh = (unsigned)(addr & 3) * 8u;
                 const uint8_t *a0 = reinterpret_cast<const uint8_t *>(addr & ~(uintptr_t)3);
@@ -487,10 +493,12 @@ extern "C" size_t b200_input_workspace_bytes(int64_t n, int src_h, int src_w, in
     return sizeof(int32_t) * (size_t)n * ((size_t)out_w * (2 + KX) + (size_t)out_h * (2 + KY)) + 3 * 256 * sizeof(float) + 16;
 }
 
-extern "C" int b200_input_crop_resize_flip_norm(const uint8_t *images, const int32_t *boxes, const uint8_t *flips,
-                                                void *out, void *workspace, size_t workspace_bytes, int64_t n,
-                                                int src_h, int src_w, int out_h, int out_w, const float *mean3,
-                                                const float *std3, int out_dtype, int out_layout, void *stream) {
+// Shared host side of the dense and the ragged entry point.  Dense: tab == nullptr, images = [n, src_h, src_w, 3].
+// Ragged: tab = int64 [n][4] on the device, src_h / src_w are upper bounds over the batch, image_bytes the slab size.
+static int input_stage_launch(const uint8_t *images, int64_t image_bytes, const int64_t *tab, const int32_t *boxes,
+                              const uint8_t *flips, void *out, void *workspace, size_t workspace_bytes, int64_t n,
+                              int src_h, int src_w, int out_h, int out_w, const float *mean3, const float *std3,
+                              int out_dtype, int out_layout, void *stream) {
     if (!images || !boxes || !out || !workspace || !mean3 || !std3) return (int)cudaErrorInvalidValue;
     if (n < 1 || src_h < 1 || src_w < 1 || out_h < 1 || out_w < 1) return (int)cudaErrorInvalidValue;
     if (out_dtype != B200_F32 && out_dtype != B200_BF16) return (int)cudaErrorInvalidValue;
@@ -519,7 +527,6 @@ extern "C" int b200_input_crop_resize_flip_norm(const uint8_t *images, const int
         const size_t smem2 = 3 * 256 * sizeof(float) + (size_t)max_rows * (src_stride + inter_stride) * sizeof(uint32_t);
         if (smem2 <= 96 * 1024) {   // larger boxes / stronger down-scaling use the generic kernel below
             const dim3 grid2((out_h + 6 + kTileRows - 1) / kTileRows, (unsigned)n);
-            const int64_t image_bytes = n * (int64_t)src_h * src_w * 3;
             cudaError_t e = cudaSuccess;
             if (out_dtype == B200_F32) {
                 auto kern = input_s2d_kernel<float>;
@@ -527,7 +534,8 @@ extern "C" int b200_input_crop_resize_flip_norm(const uint8_t *images, const int
                 if (e == cudaSuccess) e = prefer_shared(kern);
                 if (e != cudaSuccess) return (int)e;
                 kern<<<grid2, kThreads, smem2, st>>>(images, image_bytes, boxes, flips, static_cast<float *>(out), ws, lut_g,
-                                                     src_h, src_w, out_h, out_w, KX, KY, max_rows, src_stride, inter_stride);
+                                                     src_h, src_w, out_h, out_w, KX, KY, max_rows, src_stride, inter_stride,
+                                                     tab);
             } else {
                 auto kern = input_s2d_kernel<__nv_bfloat16>;
                 if (smem2 > 48 * 1024) e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2);
@@ -535,7 +543,7 @@ extern "C" int b200_input_crop_resize_flip_norm(const uint8_t *images, const int
                 if (e != cudaSuccess) return (int)e;
                 kern<<<grid2, kThreads, smem2, st>>>(images, image_bytes, boxes, flips, static_cast<__nv_bfloat16 *>(out), ws,
                                                      lut_g, src_h, src_w, out_h, out_w, KX, KY, max_rows, src_stride,
-                                                     inter_stride);
+                                                     inter_stride, tab);
             }
             B200_CHECK_LAUNCH();
             return 0;
@@ -559,7 +567,7 @@ extern "C" int b200_input_crop_resize_flip_norm(const uint8_t *images, const int
             if (e != cudaSuccess) return (int)e;
         }
         kern<<<grid, kThreads, smem, st>>>(images, boxes, flips, static_cast<float *>(out), ws, src_h, src_w, out_h,
-                                           out_w, KX, KY, max_rows, nrm, out_layout, inter_bytes);
+                                           out_w, KX, KY, max_rows, nrm, out_layout, inter_bytes, tab);
     } else {
         auto kern = input_resample_kernel<__nv_bfloat16>;
         if (smem > 48 * 1024) {
@@ -567,8 +575,71 @@ extern "C" int b200_input_crop_resize_flip_norm(const uint8_t *images, const int
             if (e != cudaSuccess) return (int)e;
         }
         kern<<<grid, kThreads, smem, st>>>(images, boxes, flips, static_cast<__nv_bfloat16 *>(out), ws, src_h, src_w,
-                                           out_h, out_w, KX, KY, max_rows, nrm, out_layout, inter_bytes);
+                                           out_h, out_w, KX, KY, max_rows, nrm, out_layout, inter_bytes, tab);
     }
+    B200_CHECK_LAUNCH();
+    return 0;
+}
+
+extern "C" int b200_input_crop_resize_flip_norm(const uint8_t *images, const int32_t *boxes, const uint8_t *flips,
+                                                void *out, void *workspace, size_t workspace_bytes, int64_t n,
+                                                int src_h, int src_w, int out_h, int out_w, const float *mean3,
+                                                const float *std3, int out_dtype, int out_layout, void *stream) {
+    if (n < 1 || src_h < 1 || src_w < 1) return (int)cudaErrorInvalidValue;
+    return input_stage_launch(images, n * (int64_t)src_h * src_w * 3, nullptr, boxes, flips, out, workspace,
+                              workspace_bytes, n, src_h, src_w, out_h, out_w, mean3, std3, out_dtype, out_layout, stream);
+}
+
+extern "C" int b200_input_crop_resize_flip_norm_ragged(const uint8_t *slab, int64_t slab_bytes, const int64_t *src_table,
+                                                       const int32_t *boxes, const uint8_t *flips, void *out,
+                                                       void *workspace, size_t workspace_bytes, int64_t n,
+                                                       int max_src_h, int max_src_w, int out_h, int out_w,
+                                                       const float *mean3, const float *std3, int out_dtype,
+                                                       int out_layout, void *stream) {
+    if (!src_table || slab_bytes < 1) return (int)cudaErrorInvalidValue;
+    if (b200_misaligned(src_table, 8)) return (int)cudaErrorMisalignedAddress;
+    return input_stage_launch(slab, slab_bytes, src_table, boxes, flips, out, workspace, workspace_bytes, n, max_src_h,
+                              max_src_w, out_h, out_w, mean3, std3, out_dtype, out_layout, stream);
+}
+
+// ---- decode staging --------------------------------------------------------------------------------
+// A JPEG decoder on the device (nvJPEG) delivers every image as three planes [3][h][w]; the input stage reads
+// interleaved RGB rows.  One launch re-packs a whole batch of planar images of different sizes into the ragged slab:
+// table row i = {address of image i's planes, h, w, byte offset of image i in the slab}; a thread moves 4 consecutive
+// pixels (12 plane bytes in, three aligned 32-bit words out), image i's pixels are dealt to the CTAs of blockIdx.y = i.
+namespace {
+__global__ void __launch_bounds__(kThreads)
+interleave_planar_kernel(const int64_t *__restrict__ table, uint8_t *__restrict__ slab) {
+    const int64_t *row = table + 4 * (int64_t)blockIdx.y;
+    const uint8_t *src = reinterpret_cast<const uint8_t *>(static_cast<uintptr_t>(row[0]));
+    const int64_t npix = row[1] * row[2];
+    uint8_t *dst = slab + row[3];
+    const uint8_t *r = src, *g = src + npix, *b = src + 2 * npix;
+    for (int64_t q = ((int64_t)blockIdx.x * kThreads + threadIdx.x) * 4; q < npix; q += (int64_t)gridDim.x * kThreads * 4) {
+        if (q + 4 <= npix) {
+            unsigned v[12];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) { v[3 * i] = r[q + i]; v[3 * i + 1] = g[q + i]; v[3 * i + 2] = b[q + i]; }
+            unsigned *o = reinterpret_cast<unsigned *>(dst + 3 * q);   // slab offsets are multiples of 16, 3q of 12
+#pragma unroll
+            for (int w = 0; w < 3; ++w)
+                o[w] = v[4 * w] | (v[4 * w + 1] << 8) | (v[4 * w + 2] << 16) | (v[4 * w + 3] << 24);
+        } else {
+            for (int64_t i = q; i < npix; ++i) { dst[3 * i] = r[i]; dst[3 * i + 1] = g[i]; dst[3 * i + 2] = b[i]; }
+        }
+    }
+}
+}  // namespace
+
+extern "C" int b200_interleave_planar_u8(const int64_t *table, uint8_t *slab, int64_t n, int64_t max_pixels,
+                                         void *stream) {
+    if (!table || !slab || n < 1 || n > 65535 || max_pixels < 1) return (int)cudaErrorInvalidValue;
+    if (b200_misaligned(table, 8) || b200_misaligned(slab)) return (int)cudaErrorMisalignedAddress;
+    int64_t per_image = (max_pixels + 4 * kThreads * 4 - 1) / (4 * kThreads * 4);   // >= 4 steps per thread
+    if (per_image > 64) per_image = 64;
+    if (per_image < 1) per_image = 1;
+    interleave_planar_kernel<<<dim3((unsigned)per_image, (unsigned)n), kThreads, 0, static_cast<cudaStream_t>(stream)>>>(
+        table, slab);
     B200_CHECK_LAUNCH();
     return 0;
 }

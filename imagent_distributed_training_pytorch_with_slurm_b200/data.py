@@ -126,11 +126,19 @@ class SyntheticImageNet:
     the compute of step i.  ``host=False`` keeps the images resident in HBM.  Images are seeded per
     rank (``seed + rank``); one fixed image batch is re-used, the crop boxes / flips / targets are
     drawn per step from the same generator unless ``fixed_params``.
+
+    ``sampler`` (a ``DistributedSampler`` over a virtual dataset of that many images; ``steps`` is then derived):
+    the epoch follows the sampler exactly as the reference's loaders follow theirs (imagenet.py:346-359,375) - this
+    rank's index stream of the current epoch cut into batches, the last one short (no ``drop_last``), the label of
+    virtual image ``i`` being ``i % num_classes``; call ``sampler.set_epoch(e)`` before each epoch.
     """
 
     def __init__(self, batch_size, steps, src_size=256, out_size=224, num_classes=1000, rank=0, seed=1234,
                  random_crop=True, mean=IMAGENET_MEAN, std=IMAGENET_STD, dtype=torch.bfloat16, host=False,
-                 fixed_params=False, device=None):
+                 fixed_params=False, device=None, sampler=None):
+        self.sampler = sampler
+        if sampler is not None:
+            steps = -(-len(sampler) // batch_size)
         self.batch_size, self.steps, self.num_classes = batch_size, steps, num_classes
         self.src_h, self.src_w = (src_size, src_size) if isinstance(src_size, int) else src_size
         self.random_crop, self.host, self.fixed_params = random_crop, host, fixed_params
@@ -148,14 +156,23 @@ class SyntheticImageNet:
             self.images = img.to(dev)
         self._fixed = None
         self._queue = None
+        self._ids = None             # sampler mode: this epoch's index batches still to be served
         self.h2d_bytes = (img.numel() if host else 0) + batch_size * (16 + 1 + 8)
-        if host:
+        if host and sampler is None:
             self._start_producer()   # the first epoch's crop parameters are being drawn while the caller sets up
 
     def __len__(self):
         return self.steps
 
+    def _epoch_batches(self):
+        ids = self.sampler.indices()
+        return [ids[i:i + self.batch_size] for i in range(0, len(ids), self.batch_size)]
+
     def _params(self):
+        if self.sampler is not None:
+            ids = self._ids.pop(0)
+            boxes, flips = draw_batch_params(len(ids), self.src_h, self.src_w, self.gen, self.random_crop)
+            return boxes.pin_memory(), flips.pin_memory(), (ids % self.num_classes).pin_memory()
         if self.fixed_params and self._fixed is not None:
             return self._fixed
         boxes, flips = draw_batch_params(self.batch_size, self.src_h, self.src_w, self.gen, self.random_crop)
@@ -185,6 +202,8 @@ class SyntheticImageNet:
         import queue
         import threading
 
+        if self.sampler is not None:
+            self._ids = self._epoch_batches()     # read the sampler's epoch NOW (set_epoch came before iter())
         q = queue.Queue(maxsize=4)
 
         def work():
@@ -210,9 +229,11 @@ class SyntheticImageNet:
     def __iter__(self):
         dev = self.stage.device
         if not self.host:
+            if self.sampler is not None:
+                self._ids = self._epoch_batches()
             for _ in range(self.steps):
                 boxes, flips, target = self._params()
-                x = self.stage(self.images, boxes, flips)
+                x = self.stage(self.images[:len(target)], boxes, flips)
                 yield x, target.to(dev, non_blocking=True)
             return
         main = torch.cuda.current_stream(dev)
@@ -224,7 +245,7 @@ class SyntheticImageNet:
             if i + 1 < self.steps:
                 self._upload(self._slots[(i + 1) % 2], i + 1 < 2, next(params))
             main.wait_event(slot["ready"])
-            x = _cabi.input_stage(slot["img"], slot["boxes"], slot["flips"], self.stage.out_h, self.stage.out_w,
+            x = _cabi.input_stage(slot["img"][:len(slot["target"])], slot["boxes"], slot["flips"], self.stage.out_h, self.stage.out_w,
                                   self.stage.mean, self.stage.std, self.stage.dtype, self.stage.layout)
             slot["free"].record(main)
             for k in ("boxes", "flips", "target"):

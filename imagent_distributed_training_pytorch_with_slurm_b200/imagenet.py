@@ -11,8 +11,10 @@ at ``epoch+1``), the best-epoch bookkeeping and the ``module.``-prefixed float32
 
 Added flags default to the reference's behaviour where it has one: ``--arch resnet18``,
 ``--image-size 448``, float32 arithmetic (``--bf16`` selects the bf16 path), cuDNN autotuning off
-(``--cudnn-benchmark`` turns it on).  ``--synthetic N`` (images per epoch) selects seeded synthetic uint8 data; the
-on-disk ``datasets.ImageNet`` front end (imagenet.py:287-296) is outside this package's scope.
+(``--cudnn-benchmark`` turns it on).  ``--data DIR`` points at the dataset (default: the reference's ``../data/imagenet``; layout
+``DIR/{train,val}/<class>/<image>``, what ``datasets.ImageNet`` reads, imagenet.py:287-296); ``--synthetic N`` (images
+per epoch) selects seeded synthetic uint8 data instead.  Either way the epoch walks this package's ``DistributedSampler``
+with ``set_epoch`` (imagenet.py:346-347,375).
 Rendezvous: the reference's SLURM variables (:225-244) when present, else torchrun's
 ``RANK/LOCAL_RANK/WORLD_SIZE``, else a single process.
 """
@@ -27,9 +29,11 @@ import torch.distributed as dist
 from . import data as b200_data
 from .ddp import FlatDDP
 from .engine import adjust_learning_rate, train, validate
+from .folder import ImageFolderIndex, ImageFolderLoader
 from .loss import CrossEntropyLoss
 from .optim import FlatSGD
 from .resnet import build_model
+from .sampler import DistributedSampler
 
 
 def _rendezvous():
@@ -81,24 +85,39 @@ def run(args):
     print(f"Backend: {dist.get_backend()}")
 
     print("Initialize Dataloaders...")
-    if not args.synthetic:
-        raise NotImplementedError(
-            "the datasets.ImageNet on-disk front end (imagenet.py:287-296) is not part of this package; "
-            "pass --synthetic <images per epoch>")
-    num_classes = 1000
+    if not args.synthetic and not args.data:
+        # the reference's hard-wired location (imagenet.py:285-289): ../data/imagenet relative to the working directory
+        args.data = os.path.join(os.path.abspath(os.path.join(".", os.pardir)), "data/imagenet")
     ref_mode = not args.random_crop
     mean, std = (b200_data.REFERENCE_MEAN, b200_data.REFERENCE_STD) if ref_mode else \
         (b200_data.IMAGENET_MEAN, b200_data.IMAGENET_STD)
     dtype = torch.bfloat16 if args.bf16 else torch.float32      # the reference trains in float32 (no autocast anywhere)
-    per_rank = -(-args.synthetic // world_size)
-    steps = -(-per_rank // args.batch_size)
-    val_steps = max(1, steps // 25)
-    common = dict(src_size=args.source_size, out_size=args.image_size, num_classes=num_classes, rank=global_rank,
-                  mean=mean, std=std, dtype=dtype, host=True)
-    train_loader = b200_data.SyntheticImageNet(args.batch_size, steps, random_crop=not ref_mode, **common)
-    val_loader = b200_data.SyntheticImageNet(args.batch_size, val_steps, random_crop=False, seed=4321, **common)
-    print("Training samples: {} images ".format(steps * args.batch_size * world_size))
-    print("Test samples: {} images ".format(val_steps * args.batch_size * world_size))
+    if args.synthetic:
+        # a virtual dataset of --synthetic images (validation: 1/25 of that), walked in DistributedSampler order
+        num_classes = 1000
+        n_train, n_val = args.synthetic, max(1, args.synthetic // 25)
+        train_sampler = DistributedSampler(n_train, num_replicas=world_size, rank=global_rank)
+        val_sampler = DistributedSampler(n_val, num_replicas=world_size, rank=global_rank)
+        common = dict(src_size=args.source_size, out_size=args.image_size, num_classes=num_classes, rank=global_rank,
+                      mean=mean, std=std, dtype=dtype, host=True)
+        train_loader = b200_data.SyntheticImageNet(args.batch_size, 0, random_crop=not ref_mode, sampler=train_sampler,
+                                                   **common)
+        val_loader = b200_data.SyntheticImageNet(args.batch_size, 0, random_crop=False, seed=4321, sampler=val_sampler,
+                                                 **common)
+    else:
+        # datasets.ImageNet(root, split) x2, DistributedSampler x2, DataLoader x2 (imagenet.py:293-296,346-359)
+        trainset = ImageFolderIndex(args.data, "train")
+        valset = ImageFolderIndex(args.data, "val")
+        num_classes = len(trainset.classes)
+        n_train, n_val = len(trainset), len(valset)
+        train_sampler = DistributedSampler(trainset, num_replicas=world_size, rank=global_rank)
+        val_sampler = DistributedSampler(valset, num_replicas=world_size, rank=global_rank)
+        common = dict(out_size=args.image_size, mean=mean, std=std, dtype=dtype, decoder=args.decoder,
+                      workers=args.workers, rank=global_rank)
+        train_loader = ImageFolderLoader(trainset, train_sampler, args.batch_size, random_crop=not ref_mode, **common)
+        val_loader = ImageFolderLoader(valset, val_sampler, args.batch_size, random_crop=False, **common)
+    print("Training samples: {} images ".format(n_train))
+    print("Test samples: {} images ".format(n_val))
     print("number of classes: {}".format(num_classes))
 
     print("Initialize Model...")
@@ -118,6 +137,7 @@ def run(args):
     best_epoch_top1 = best_epoch_top5 = 0
     ckpt = "imagenet_FR_resnet18.pt" if args.arch == "resnet18" else f"imagenet_FR_{args.arch}.pt"
     for epoch in range(args.epochs):
+        train_sampler.set_epoch(epoch)            # imagenet.py:375 (the validation sampler stays at epoch 0, as there)
         lr = adjust_learning_rate(args.lr, optimizer, epoch)
         train_loss, train_prec1, train_prec5, epoch_t1 = train(train_loader, model, criterion, optimizer, epoch,
                                                                world_size)
@@ -166,6 +186,13 @@ def build_parser():
     parser.add_argument("--image-size", type=int, default=448, help="network input size (reference: 448)")
     parser.add_argument("--source-size", type=int, default=500, help="synthetic source image size")
     parser.add_argument("--synthetic", type=int, default=0, metavar="IMAGES", help="synthetic images per epoch")
+    parser.add_argument("--data", type=str, default=None, metavar="DIR",
+                        help="dataset root holding train/<class>/*.JPEG and val/<class>/*.JPEG, i.e. what "
+                             "datasets.ImageNet reads after extraction (default: the reference's ../data/imagenet)")
+    parser.add_argument("--decoder", type=str, default="pil", choices=["pil", "nvjpeg"],
+                        help="JPEG decoding: Pillow in host threads (the reference's pixels) or nvJPEG on the GPU")
+    parser.add_argument("--workers", type=int, default=10, help="host threads reading / decoding files (reference: 10 "
+                                                                "DataLoader workers)")
     parser.add_argument("--random-crop", action="store_true", default=False,
                         help="RandomResizedCrop + horizontal flip + ImageNet mean/std instead of the reference's "
                              "plain resize and 0.5/0.5 normalisation")

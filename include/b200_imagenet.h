@@ -226,6 +226,31 @@ int b200_input_crop_resize_flip_norm(const uint8_t *images, const int32_t *boxes
                                      int out_h, int out_w, const float *mean3, const float *std3, int out_dtype,
                                      int out_layout, void *stream);
 
+/* K1 on a RAGGED batch: the images of a real dataset have different sizes (the reference resizes each PIL image on
+ * its own, imagenet.py:280-283,293-296), so the decoded batch is one byte slab with a table instead of a dense
+ * [n,h,w,3] tensor:
+ *   slab      : uint8, slab_bytes long; image i is interleaved RGB with rows src_table[4i+3] bytes apart
+ *   src_table : int64 [n,4] on the DEVICE, rows (byte offset of the image in the slab, height, width, row pitch)
+ *   boxes     : as above, each inside ITS image (whole image = (0, 0, height, width): the reference's Resize)
+ *   max_src_h / max_src_w : upper bounds of the heights / widths in the batch (they size the tap tables and the
+ *               shared-memory staging; workspace = b200_input_workspace_bytes(n, max_src_h, max_src_w, ...));
+ *               the 8x down-scaling limit applies to them.
+ * Same arithmetic, same kernels and the same output layouts as the dense entry point. */
+int b200_input_crop_resize_flip_norm_ragged(const uint8_t *slab, int64_t slab_bytes, const int64_t *src_table,
+                                            const int32_t *boxes, const uint8_t *flips, void *out, void *workspace,
+                                            size_t workspace_bytes, int64_t n, int max_src_h, int max_src_w, int out_h,
+                                            int out_w, const float *mean3, const float *std3, int out_dtype,
+                                            int out_layout, void *stream);
+
+/* Decode staging for the ragged input stage.  The reference decodes JPEGs with PIL inside the DataLoader workers
+ * (datasets.ImageNet -> pil_loader, imagenet.py:293-296,350-359); here the bytes can be decoded on the device by
+ * nvJPEG (a library), which returns every image as three planes [3,h,w].  This re-packs a batch of such planar images
+ * into the interleaved slab b200_input_crop_resize_flip_norm_ragged reads, in one launch:
+ *   table : int64 [n,4] on the DEVICE, rows (device address of the planar image, height, width, byte offset of the
+ *           image in the slab - a multiple of 16; rows are packed, pitch = 3*width)
+ *   max_pixels : largest height*width in the batch (sizes the grid). */
+int b200_interleave_planar_u8(const int64_t *table, uint8_t *slab, int64_t n, int64_t max_pixels, void *stream);
+
 /* ------------------------------------------------------------------------------------------------
  * K6  3x3 / stride 2 / pad 1 max-pooling, channels-last, forward and backward.
  * Replaces nn.MaxPool2d(kernel_size=3, stride=2, padding=1) after the stem (torchvision
