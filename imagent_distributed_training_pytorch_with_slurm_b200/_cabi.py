@@ -10,6 +10,8 @@ import threading
 
 import torch
 
+from . import _nvtx
+
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libb200_imagenet.so")
 
@@ -563,10 +565,12 @@ def input_stage(images, boxes, flips, out_h, out_w, mean, std, out_dtype=torch.b
     mean3 = (_f32 * 3)(*[float(v) for v in mean])
     std3 = (_f32 * 3)(*[float(v) for v in std])
     s = stats.begin("input")
-    _check(lib.b200_input_crop_resize_flip_norm(_ptr(images), _ptr(boxes), _ptr(flips), _ptr(out), _ptr(ws), ws.numel(),
+    _nvtx.push("b200.input")
+    rc = (lib.b200_input_crop_resize_flip_norm(_ptr(images), _ptr(boxes), _ptr(flips), _ptr(out), _ptr(ws), ws.numel(),
                                                 n, sh, sw, out_h, out_w, mean3, std3,
-                                                F32 if out_dtype == torch.float32 else BF16, layout, _stream()),
-           "b200_input_crop_resize_flip_norm")
+                                                F32 if out_dtype == torch.float32 else BF16, layout, _stream()))
+    _nvtx.pop()
+    _check(rc, "b200_input_crop_resize_flip_norm")
     stats.end("input", 2, s, n * 3 * out_h * out_w * out.element_size())  # + box bytes, added by the caller
     return out
 

@@ -19,6 +19,8 @@
 // Variance: each chunk accumulates sums shifted by the chunk's first row (sum(x-K), sum((x-K)^2)),
 // converts to (mean_b, M2_b) and the finalize combines chunks with the pairwise-update formula
 // (M2 = sum M2_b + n_b (mean_b - mean)^2), so there is no E[x^2]-E[x]^2 cancellation.
+#include <cooperative_groups.h>
+
 #include "common.cuh"
 
 namespace {
@@ -36,6 +38,8 @@ int g_bn_pipeline = 1;       // 1 = bulk-async (TMA) shared-memory ring kernels 
 int g_bn_pipe_ctas_per_sm = 2;
 int g_bn_pipe_stages = 0;    // 0 = automatic
 int g_bn_pdl = 1;            // finalize / apply kernels of the bulk-async path use programmatic dependent launch
+int g_bn_fused = 0;          // 1 = one cooperative kernel per site (bn_fused.cuh) where the shape allows, 0 = the chain.
+                             // Off by default: measured SLOWER than the chain on every ResNet-50 shape (see bn_fused.cuh)
 
 template <typename T, int VEC>
 struct Unroll {
@@ -111,6 +115,7 @@ __device__ __forceinline__ void cta_reduce_rows(float (&val)[NV], int tx, float 
 }
 
 #include "bn_pipe.cuh"
+#include "bn_fused.cuh"
 
 // Geometry of the bulk-async kernels: every CTA owns whole rows (TX = CV <= 256), tiles of kTileVecs
 // vectors.  The number of chunks is one wave of resident CTAs (148 x g_bn_pipe_ctas_per_sm), capped
@@ -178,6 +183,65 @@ cudaError_t launch(void (*kern)(KArgs...), unsigned grid, size_t smem, cudaStrea
     cfg.attrs = attr;
     cfg.numAttrs = (dependent && g_bn_pdl) ? 1 : 0;
     return cudaLaunchKernelEx(&cfg, kern, static_cast<KArgs>(args)...);
+}
+
+// Cooperative launch (grid-wide barriers inside the kernel): the whole grid must be resident at once.
+template <typename... KArgs, typename... Args>
+cudaError_t launch_coop(void (*kern)(KArgs...), unsigned grid, size_t smem, cudaStream_t st, Args... args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(grid);
+    cfg.blockDim = dim3(kThreads);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeCooperative;
+    attr[0].val.cooperative = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    return cudaLaunchKernelEx(&cfg, kern, static_cast<KArgs>(args)...);
+}
+
+// How many CTAs of `kern` with `smem` dynamic bytes fit on the device at once (0 on error); cached per (kernel, smem).
+// (The dynamic-shared-memory attribute it sets for the query is per kernel, not per size: callers set it again before
+// every launch, as the chain's launches do.)
+template <typename K>
+int coop_capacity(K kern, size_t smem) {
+    struct Entry { const void *k; size_t smem; int dev; int cap; };
+    static Entry cache[64];
+    static int used = 0;
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess) return 0;
+    const void *key = reinterpret_cast<const void *>(kern);
+    for (int i = 0; i < used; ++i)
+        if (cache[i].k == key && cache[i].smem == smem && cache[i].dev == dev) return cache[i].cap;
+    if (allow_smem(kern, smem) != cudaSuccess) return 0;
+    int per_sm = 0, sms = 0;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, kThreads, smem) != cudaSuccess) return 0;
+    if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess) return 0;
+    const int cap = per_sm * sms;
+    if (used < 64) cache[used++] = Entry{key, smem, dev, cap};
+    return cap;
+}
+
+// Geometry of a fused (two-pass, cooperative) site: one chunk per CTA for both passes, at most `cap` CTAs.
+struct FusedGeom {
+    Geom g;
+    int stages1, stages2;
+    size_t smem;
+};
+
+FusedGeom make_geom_fused(int64_t m, int c, int vec, int esize, int nt1, bool mask1, int nt2, bool mask2,
+                          size_t static_smem) {
+    FusedGeom fg;
+    const bool first_larger = pipe_stage_bytes(nt1, mask1) >= pipe_stage_bytes(nt2, mask2);
+    const PipeGeom big = make_geom_pipe(m, c, vec, esize, first_larger ? nt1 : nt2, first_larger ? mask1 : mask2, static_smem);
+    fg.g = big.g;
+    fg.smem = big.smem;
+    const size_t data = big.smem - 128;
+    int s1 = (int)(data / pipe_stage_bytes(nt1, mask1)), s2 = (int)(data / pipe_stage_bytes(nt2, mask2));
+    fg.stages1 = s1 > kMaxStages ? kMaxStages : s1;
+    fg.stages2 = s2 > kMaxStages ? kMaxStages : s2;
+    return fg;
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -514,6 +578,30 @@ int fwd_train_impl(const void *x_, const void *z_, void *y_, uint8_t *mask, cons
     T *y = static_cast<T *>(y_);
     if constexpr (VEC * sizeof(T) == 16) if (pipe_eligible(c, VEC, sizeof(T))) {
         const size_t red_bytes = sizeof(float) * kThreads * 2 * VEC;
+        if (g_bn_fused) {
+            // one cooperative kernel: statistics, fold and apply (bn_fused.cuh)
+            const int nt2 = (y && act == B200_ACT_ADD_RELU) ? 2 : 1;
+            const FusedGeom fg = make_geom_fused(m, c, VEC, sizeof(T), 1, false, nt2, false, red_bytes);
+            const Geom &g = fg.g;
+            if (ws_bytes < ws_bytes_for(g, c)) return (int)cudaErrorInvalidValue;
+            const Ws w = carve(ws, g, c);
+            cudaError_t e = cudaErrorUnknown;
+#define B200_FWD_FUSED(ACT)                                                                                       \
+    do {                                                                                                          \
+        auto k = bn_fwd_fused_kernel<T, VEC, ACT>;                                                                \
+        if (coop_capacity(k, fg.smem) >= g.nchunk && allow_smem(k, fg.smem) == cudaSuccess)                       \
+            e = launch_coop(k, g.nchunk, fg.smem, st, x, z, y, mask, w.partial, gamma, beta, rm, rv, nbt, saved,  \
+                            saved2, eps, momentum, m, c, g.txl, g.nchunk, g.rpc, fg.stages1, fg.stages2);         \
+    } while (0)
+            if (!y || act == B200_ACT_NONE) B200_FWD_FUSED(B200_ACT_NONE);
+            else if (act == B200_ACT_RELU) B200_FWD_FUSED(B200_ACT_RELU);
+            else B200_FWD_FUSED(B200_ACT_ADD_RELU);
+#undef B200_FWD_FUSED
+            if (e == cudaSuccess) return 0;
+            if (e == cudaErrorCooperativeLaunchTooLarge) (void)cudaGetLastError();   // nothing was launched
+            else if (e != cudaErrorUnknown) return (int)e;
+            // grid does not fit at once on this device: the three-kernel chain below
+        }
         const PipeGeom ps = make_geom_pipe(m, c, VEC, sizeof(T), 1, false, red_bytes);
         const Geom &g = ps.g;
         if (ws_bytes < ws_bytes_for(g, c)) return (int)cudaErrorInvalidValue;
@@ -623,6 +711,33 @@ int bwd_impl(const void *dy_, const void *dy2_, const void *x_, const uint8_t *m
         const size_t red_bytes = sizeof(float) * kThreads * 2 * VEC;
         const bool masked = act == B200_ACT_ADD_RELU;
         const int nt = dy2 ? 3 : 2;
+        if (g_bn_fused) {
+            const FusedGeom fg = make_geom_fused(m, c, VEC, sizeof(T), nt, masked, nt, masked, red_bytes);
+            const Geom &g = fg.g;
+            if (ws_bytes < ws_bytes_for(g, c)) return (int)cudaErrorInvalidValue;
+            const Ws w = carve(ws, g, c);
+            cudaError_t e = cudaErrorUnknown;
+#define B200_BWD_FUSED2(ACT, DY2)                                                                                 \
+    do {                                                                                                          \
+        auto k = bn_bwd_fused_kernel<T, VEC, ACT, DY2>;                                                           \
+        if (coop_capacity(k, fg.smem) >= g.nchunk && allow_smem(k, fg.smem) == cudaSuccess)                       \
+            e = launch_coop(k, g.nchunk, fg.smem, st, dy, dy2, x, mask, gamma, saved, w.partial, w.coef, dgamma,  \
+                            dbeta, dx, dz, m, c, g.txl, g.nchunk, g.rpc, fg.stages1);                             \
+    } while (0)
+#define B200_BWD_FUSED(ACT)                                                                                       \
+    do {                                                                                                          \
+        if (dy2) B200_BWD_FUSED2(ACT, true);                                                                      \
+        else B200_BWD_FUSED2(ACT, false);                                                                         \
+    } while (0)
+            if (act == B200_ACT_NONE) B200_BWD_FUSED(B200_ACT_NONE);
+            else if (act == B200_ACT_RELU) B200_BWD_FUSED(B200_ACT_RELU);
+            else B200_BWD_FUSED(B200_ACT_ADD_RELU);
+#undef B200_BWD_FUSED
+#undef B200_BWD_FUSED2
+            if (e == cudaSuccess) return 0;
+            if (e == cudaErrorCooperativeLaunchTooLarge) (void)cudaGetLastError();   // nothing was launched: the chain
+            else if (e != cudaErrorUnknown) return (int)e;
+        }
         const PipeGeom pr = make_geom_pipe(m, c, VEC, sizeof(T), nt, masked, red_bytes);
         const PipeGeom pa = make_geom_pipe(m, c, VEC, sizeof(T), nt, masked, 0);
         const Geom &g = pr.g;
@@ -748,6 +863,7 @@ extern "C" int b200_tune_set(const char *key, int value) {
     if (eq("bn_apply_reverse")) { g_bn_apply_reverse = value != 0; return 0; }
     if (eq("bn_pipeline")) { g_bn_pipeline = value != 0; return 0; }
     if (eq("bn_pdl")) { g_bn_pdl = value != 0; return 0; }
+    if (eq("bn_fused")) { g_bn_fused = value != 0; return 0; }
     if (eq("input_s2d_fast")) { g_input_s2d_fast = value != 0; return 0; }
     if (eq("bn_pipe_stages")) { if (value < 0 || value > kMaxStages || value == 1) return (int)cudaErrorInvalidValue; g_bn_pipe_stages = value; return 0; }
     if (eq("bn_pipe_ctas_per_sm")) { if (value < 1 || value > 8) return (int)cudaErrorInvalidValue; g_bn_pipe_ctas_per_sm = value; return 0; }

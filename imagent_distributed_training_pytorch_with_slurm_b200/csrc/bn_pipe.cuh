@@ -86,8 +86,11 @@ struct TileRing {
     }
     __device__ __forceinline__ unsigned char *mstage(int s) const { return msk + (size_t)s * kTileVecs; }
 
-    __device__ void setup(unsigned char *smem, int txl, int nstages, int64_t c_bytes, int64_t r0_, int64_t r1_) {
-        bars = reinterpret_cast<uint64_t *>(smem);
+    // bar_off: which of the two barrier sets of the 128-byte header to use (0 or 64) - a kernel that walks its rows
+    // twice re-arms the ring on the second set instead of re-initialising barriers that may still be in use
+    __device__ void setup(unsigned char *smem, int txl, int nstages, int64_t c_bytes, int64_t r0_, int64_t r1_,
+                          int bar_off = 0) {
+        bars = reinterpret_cast<uint64_t *>(smem + bar_off);
         data = smem + 128;
         stages = nstages;
         msk = data + (size_t)nstages * NT * kTileVecs * 16;

@@ -37,24 +37,34 @@ __global__ void __launch_bounds__(kThreads) pack_grads_kernel(const __grid_const
     const long long n = tab.cnt[t];
     const long long n8 = n >> 3;
     const long long v0 = (long long)((int)blockIdx.x - tab.first_block[t]) * (kBlockElems / 8);
+    constexpr int kSteps = kBlockElems / 8 / kThreads;
+    // all of a thread's loads are issued before its first store (the sources are dead after this kernel: streaming
+    // loads; the arena is read next by the all-reduce / the optimizer: ordinary stores, it stays in L2)
+    float e[kSteps][8];
 #pragma unroll
-    for (int step = 0; step < kBlockElems / 8 / kThreads; ++step) {
+    for (int step = 0; step < kSteps; ++step) {
         const long long v = v0 + step * kThreads + threadIdx.x;
-        if (v >= n8) break;
-        float e[8];
-        if constexpr (sizeof(T) == 2) {
-            VecIO<__nv_bfloat16, 8>::load(reinterpret_cast<const __nv_bfloat16 *>(src) + v * 8, e);
-        } else {
-            float a[4], b[4];
-            VecIO<float, 4>::load(reinterpret_cast<const float *>(src) + v * 8, a);
-            VecIO<float, 4>::load(reinterpret_cast<const float *>(src) + v * 8 + 4, b);
+        if (v < n8) {
+            if constexpr (sizeof(T) == 2) {
+                VecIO<__nv_bfloat16, 8>::load_stream(reinterpret_cast<const __nv_bfloat16 *>(src) + v * 8, e[step]);
+            } else {
+                float a[4], b[4];
+                VecIO<float, 4>::load_stream(reinterpret_cast<const float *>(src) + v * 8, a);
+                VecIO<float, 4>::load_stream(reinterpret_cast<const float *>(src) + v * 8 + 4, b);
 #pragma unroll
-            for (int k = 0; k < 4; ++k) { e[k] = a[k]; e[4 + k] = b[k]; }
+                for (int k = 0; k < 4; ++k) { e[step][k] = a[k]; e[step][4 + k] = b[k]; }
+            }
         }
-        float a[4] = {e[0] * scale, e[1] * scale, e[2] * scale, e[3] * scale};
-        float b[4] = {e[4] * scale, e[5] * scale, e[6] * scale, e[7] * scale};
-        VecIO<float, 4>::store(out + v * 8, a);
-        VecIO<float, 4>::store(out + v * 8 + 4, b);
+    }
+#pragma unroll
+    for (int step = 0; step < kSteps; ++step) {
+        const long long v = v0 + step * kThreads + threadIdx.x;
+        if (v < n8) {
+            float a[4] = {e[step][0] * scale, e[step][1] * scale, e[step][2] * scale, e[step][3] * scale};
+            float b[4] = {e[step][4] * scale, e[step][5] * scale, e[step][6] * scale, e[step][7] * scale};
+            VecIO<float, 4>::store(out + v * 8, a);
+            VecIO<float, 4>::store(out + v * 8 + 4, b);
+        }
     }
     if ((int)blockIdx.x == tab.first_block[t] && threadIdx.x < (n & 7)) {   // ragged tail, by the tensor's first CTA
         const long long i = (n8 << 3) + threadIdx.x;

@@ -21,6 +21,8 @@ import torch
 import torch.distributed as dist
 import torch.nn as nn
 
+from . import _nvtx
+
 
 class FlatDDP(nn.Module):
     def __init__(self, module, device_ids=None, output_device=None, process_group=None, bucket_cap_mb=25,
@@ -122,11 +124,13 @@ class FlatDDP(nn.Module):
         g = self.module.arena.grads
         while self._next < len(self.buckets) and self.buckets[self._next][0] >= offset:
             lo, hi = self.buckets[self._next]
+            _nvtx.push("b200.exchange")
             if self.exchange == "peer":
                 self._peer_bucket(self._next, lo, hi)
             else:
                 self._works.append(dist.all_reduce(g[lo:hi], op=dist.ReduceOp.SUM, group=self.process_group,
                                                    async_op=True))
+            _nvtx.pop()
             self._next += 1
 
     def backward_done(self):

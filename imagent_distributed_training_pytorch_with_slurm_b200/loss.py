@@ -8,7 +8,7 @@ imagenet.py:124,134) reuses that result instead of launching again.
 import torch
 import torch.nn as nn
 
-from . import _cabi
+from . import _cabi, _nvtx
 
 # most recent (logits, target) pair and its result; holding the tensors keeps their memory from
 # being handed to another tensor, so a pointer match means "the same batch" - as long as nobody wrote into
@@ -59,11 +59,12 @@ class CrossEntropyLoss(nn.Module):
         if logits.dim() != 2:
             raise ValueError("expected [N, C] logits")
         logits = logits if logits.is_contiguous() else logits.contiguous()
-        if torch.is_grad_enabled() and logits.requires_grad:
-            return _CEFn.apply(logits, target)
-        out3, _ = _cabi.ce_topk_fwd(logits, target)
-        _remember(logits, target, out3)
-        return out3[0]
+        with _nvtx.range("b200.loss"):
+            if torch.is_grad_enabled() and logits.requires_grad:
+                return _CEFn.apply(logits, target)
+            out3, _ = _cabi.ce_topk_fwd(logits, target)
+            _remember(logits, target, out3)
+            return out3[0]
 
     @staticmethod
     def last_metrics():

@@ -8,7 +8,7 @@ momentum and the update (and refreshes the bf16 shadow weights) instead of four 
 import torch
 from torch.optim.optimizer import Optimizer
 
-from . import _cabi
+from . import _cabi, _nvtx
 
 
 class FlatSGD(Optimizer):
@@ -46,8 +46,9 @@ class FlatSGD(Optimizer):
         if a.applied_step == a.steps:   # FlatDDP(exchange="peer") updated every shard inside the backward
             a.steps += 1
             return None
-        _cabi.sgd_flat(a.params, a.grads, a.momentum, a.shadow, float(g["lr"]), float(g["weight_decay"]),
-                       float(g["momentum"]), 1.0, a.steps == 0)
+        with _nvtx.range("b200.step"):
+            _cabi.sgd_flat(a.params, a.grads, a.momentum, a.shadow, float(g["lr"]), float(g["weight_decay"]),
+                           float(g["momentum"]), 1.0, a.steps == 0)
         a.steps += 1
         return None
 

@@ -26,7 +26,7 @@ import math
 import torch
 import torch.nn as nn
 
-from . import _cabi
+from . import _cabi, _nvtx
 
 _ALIGN = 32  # floats: every parameter starts on a 128-byte boundary of the arena
 # resolved overloads: calling the packet (torch.ops.aten.convolution) re-resolves the overload on every call
@@ -486,6 +486,10 @@ class B200ResNet(nn.Module):
         return self._forward_eval(x)
 
     def _forward_train(self, x):
+        with _nvtx.range("b200.forward"):
+            return self._forward_train_impl(x)
+
+    def _forward_train_impl(self, x):
         stem = self._stem(x)
         tape = {"x0": x, "stem": stem}
         t = stem.fwd(x)
@@ -520,6 +524,10 @@ class B200ResNet(nn.Module):
         self.arena.grads_pending = False
 
     def _backward(self, tape, g_logits):
+        with _nvtx.range("b200.backward"):
+            return self._backward_impl(tape, g_logits)
+
+    def _backward_impl(self, tape, g_logits):
         if self.arena.grads_pending:
             raise RuntimeError(
                 "backward() called twice without optimizer.zero_grad() or optimizer.step() in between: this model "

@@ -248,6 +248,39 @@ def test_bn_bf16_matches_oracle(m, c, act, vec):
         cabi.tune_set("bn_vec_bf16", 8)
 
 
+@pytest.mark.parametrize("m,c", [(4096, 64), (12544, 256), (3001, 128), (1568, 2048), (50176, 64)])
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_bn_single_kernel_form_is_bit_identical_to_the_three_kernel_chain(m, c, dtype):
+    """The cooperative one-kernel-per-site form (statistics / fold / apply with grid-wide barriers inside) uses the
+    chain's chunking, partial layout and summation order, so every output must have the same bits: forward (none,
+    relu, add+relu, statistics only), running statistics, backward with and without a second gradient branch."""
+    cabi.tune_set("bn_vec_bf16", 8)
+    g = torch.Generator().manual_seed(m + c)
+    mk = lambda: (torch.randn(m, c, generator=g) * 1.5 + 0.3).to(dtype).to(DEV).view(1, m, 1, c).permute(0, 3, 1, 2)  # noqa: E731
+    x, z, dy, dy2 = mk(), mk(), mk(), mk()
+    gamma, beta = torch.rand(c, generator=g).add(0.5).to(DEV), torch.randn(c, generator=g).to(DEV)
+    res = []
+    for fused in (0, 1):
+        cabi.tune_set("bn_fused", fused)
+        out = []
+        for act, zz in ((cabi.ACT_NONE, None), (cabi.ACT_RELU, None), (cabi.ACT_ADD_RELU, z)):
+            rm, rv = torch.zeros(c, device=DEV), torch.ones(c, device=DEV)
+            nbt = torch.zeros((), dtype=torch.int64, device=DEV)
+            y, saved, mask = cabi.bn_fwd_train(x, zz, gamma, beta, rm, rv, nbt, 1e-5, 0.1, act)
+            out += [y, saved, rm, rv, nbt] + ([mask[:-16]] if mask is not None else [])
+            for second in (None, dy2):
+                dx, dz, dg, db = cabi.bn_bwd(dy, x, mask, gamma, saved, act, dy2=second)
+                out += [dx, dg, db] + ([dz] if dz is not None else [])
+        rm, rv = torch.zeros(c, device=DEV), torch.ones(c, device=DEV)
+        out += [cabi.bn_stats(x, gamma, beta, rm, rv, None, 1e-5, 0.1), rm, rv]
+        torch.cuda.synchronize()
+        res.append([t.clone() for t in out])
+    cabi.tune_set("bn_fused", 0)      # the default (the single-kernel form measured slower, see csrc/bn_fused.cuh)
+    assert len(res[0]) == len(res[1])
+    for i, (a, b) in enumerate(zip(*res)):
+        assert torch.equal(a, b), i
+
+
 def test_bn_golden_case_from_torch():
     c = np.load(os.path.join(GOLD, "bn_case.npz"))
 
