@@ -42,6 +42,7 @@ SIGNATURES = {
     "b200_bn_bwd": (_i32, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _sz, _i64, _i32, _i32, _i32, _vp]),
     "b200_maxpool3x3s2_fwd": (_i32, [_vp, _vp, _vp, _i64, _i32, _i32, _i32, _i32, _vp]),
     "b200_maxpool3x3s2_bwd": (_i32, [_vp, _vp, _vp, _vp, _i64, _i32, _i32, _i32, _i32, _vp]),
+    "b200_bn_relu_maxpool3x3s2_fwd": (_i32, [_vp, _vp, _vp, _vp, _i64, _i32, _i32, _i32, _i32, _vp]),
     "b200_bn_dual_supported": (_i32, [_i32, _i32]),
     "b200_bn_stats": (_i32, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _sz, _i64, _i32, _f32, _f32, _i32, _vp]),
     "b200_bn_fwd_train_dual": (_i32, [_vp] * 12 + [_sz, _i64, _i32, _f32, _f32, _i32, _vp]),
@@ -477,6 +478,28 @@ def maxpool_fwd(x):
     _check(load().b200_maxpool3x3s2_fwd(_ptr(x), _ptr(y), _ptr(arg), n, c, h, w, dtype_code(x), _stream()),
            "b200_maxpool3x3s2_fwd")
     stats.end("maxpool_fwd", 1, s, x.numel() * x.element_size() + y.numel() * (x.element_size() + 1))
+    return y, arg
+
+
+def bn_relu_maxpool_fwd(x, saved):
+    """max-pool(relu(x * scale + shift)) with ``saved`` = float32 [4,C] of ``bn_stats`` / ``bn_fwd_train`` (rows 2, 3 =
+    scale, shift): the stem's BatchNorm apply + ReLU + pool in one pass, bit-identical to the two kernels run one after
+    the other, without the normalised activation ever touching memory.  Returns (y, argmax)."""
+    _need_cuda(x, saved)
+    if x.dim() != 4 or not x.is_contiguous(memory_format=torch.channels_last):
+        raise B200Error("max-pool kernel needs a channels-last 4-d activation")
+    n, c, h, w = x.shape
+    if saved.dtype != torch.float32 or tuple(saved.shape) != (4, c) or not saved.is_contiguous():
+        raise B200Error("saved must be the float32 [4,C] statistics tensor of the BatchNorm forward")
+    oh, ow = (h - 1) // 2 + 1, (w - 1) // 2 + 1
+    y = torch.empty((n, c, oh, ow), dtype=x.dtype, device=x.device, memory_format=torch.channels_last)
+    arg = torch.empty((n, oh, ow, c), dtype=torch.uint8, device=x.device)
+    s = stats.begin("maxpool_fwd")
+    _check(load().b200_bn_relu_maxpool3x3s2_fwd(_ptr(x), saved.data_ptr() + 2 * c * 4, _ptr(y), _ptr(arg), n, c, h, w,
+                                                dtype_code(x), _stream()), "b200_bn_relu_maxpool3x3s2_fwd")
+    nbytes = x.numel() * x.element_size() + y.numel() * (x.element_size() + 1)
+    # SURVEY 8d counts this work as the apply pass of a bn+relu site (2 E*s) plus the pool (x + y + argmax)
+    stats.end("maxpool_fwd", 1, s, nbytes, nbytes + 2 * x.numel() * x.element_size())
     return y, arg
 
 

@@ -40,10 +40,21 @@ struct V8<float> {
     }
 };
 
+// Rounds to the activation type and back: the fused stem kernel must pool over exactly the values the separate
+// BatchNorm+ReLU kernel would have STORED.
 template <typename T>
+__device__ __forceinline__ float round_to(float v);
+template <>
+__device__ __forceinline__ float round_to<float>(float v) { return v; }
+template <>
+__device__ __forceinline__ float round_to<__nv_bfloat16>(float v) { return __bfloat162float(__float2bfloat16_rn(v)); }
+
+// AFFINE: every tap is first mapped through relu(x * scale[ch] + shift[ch]) (the BatchNorm+ReLU in front of the pool,
+// torchvision resnet.py:269-270), so the normalised 4x larger activation is never written or read.
+template <typename T, bool AFFINE>
 __global__ void __launch_bounds__(kThreads)
 maxpool_fwd_kernel(const T *__restrict__ x, T *__restrict__ y, uint8_t *__restrict__ arg, int64_t total, int c8, int h,
-                   int w, int oh, int ow) {
+                   int w, int oh, int ow, const float *__restrict__ scale_shift) {
     const int64_t gid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (gid >= total) return;
     const int cv = (int)(gid % c8);
@@ -54,8 +65,14 @@ maxpool_fwd_kernel(const T *__restrict__ x, T *__restrict__ y, uint8_t *__restri
     const int c = c8 * 8;
     float best[8];
     unsigned pos[8];
+    float sc[8], sf[8];
 #pragma unroll
-    for (int k = 0; k < 8; ++k) { best[k] = -INFINITY; pos[k] = 0; }
+    for (int k = 0; k < 8; ++k) {
+        best[k] = -INFINITY;
+        pos[k] = 0;
+        sc[k] = AFFINE ? scale_shift[cv * 8 + k] : 1.f;
+        sf[k] = AFFINE ? scale_shift[c + cv * 8 + k] : 0.f;
+    }
     bool first = true;
 #pragma unroll
     for (int kh = 0; kh < 3; ++kh) {
@@ -67,6 +84,10 @@ maxpool_fwd_kernel(const T *__restrict__ x, T *__restrict__ y, uint8_t *__restri
             if (ix < 0 || ix >= w) continue;
             float v[8];
             V8<T>::load(x + ((n * h + iy) * w + ix) * c + cv * 8, v);
+            if (AFFINE) {
+#pragma unroll
+                for (int k = 0; k < 8; ++k) v[k] = round_to<T>(fmaxf(fmaf(v[k], sc[k], sf[k]), 0.f));   // bn_apply's form
+            }
 #pragma unroll
             for (int k = 0; k < 8; ++k) {
                 if (first || v[k] > best[k] || v[k] != v[k]) { best[k] = v[k]; pos[k] = kh * 3 + kw; }
@@ -177,9 +198,11 @@ __device__ __forceinline__ __nv_bfloat162 as_bf162(unsigned u) {
 }
 __device__ __forceinline__ unsigned as_u32(__nv_bfloat162 v) { return *reinterpret_cast<unsigned *>(&v); }
 
+template <bool AFFINE>
 __global__ void __launch_bounds__(kThreads)
 maxpool_fwd_bf16_kernel(const __nv_bfloat16 *__restrict__ x, __nv_bfloat16 *__restrict__ y, uint8_t *__restrict__ arg,
-                        unsigned total, FastDiv dc8, FastDiv dow, FastDiv doh, int h, int w) {
+                        unsigned total, FastDiv dc8, FastDiv dow, FastDiv doh, int h, int w,
+                        const float *__restrict__ scale_shift) {
     const unsigned gid = blockIdx.x * kThreads + threadIdx.x;
     if (gid >= total) return;
     const int c8 = (int)dc8.d;
@@ -194,7 +217,8 @@ maxpool_fwd_bf16_kernel(const __nv_bfloat16 *__restrict__ x, __nv_bfloat16 *__re
     const int rs = w * c8;  // uint4 units; one image row always fits 32 bits here (total < 2^31)
     const unsigned ninf = 0xff80ff80u;
     uint4 v[9];
-    if (iy0 >= 0 && ix0 >= 0 && iy0 + 2 < h && ix0 + 2 < w) {
+    const bool interior = iy0 >= 0 && ix0 >= 0 && iy0 + 2 < h && ix0 + 2 < w;
+    if (interior) {
 #pragma unroll
         for (int kh = 0; kh < 3; ++kh)
 #pragma unroll
@@ -208,6 +232,30 @@ maxpool_fwd_bf16_kernel(const __nv_bfloat16 *__restrict__ x, __nv_bfloat16 *__re
                 v[kh * 3 + kw] = make_uint4(ninf, ninf, ninf, ninf);
                 if (ok) v[kh * 3 + kw] = __ldg(base + kh * rs + kw * c8);
             }
+    }
+    if (AFFINE) {
+        // relu(x * scale + shift) in float32 exactly as the BatchNorm apply kernel does it, rounded once to bf16 - the
+        // values that kernel would have stored; taps outside the image stay -inf.  (fmaxf maps NaN to 0, as there.)
+        float sc[8], sf[8];
+        const int cch = c8 * 8;
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+            sc[k] = __ldg(scale_shift + cv * 8 + k);
+            sf[k] = __ldg(scale_shift + cch + cv * 8 + k);
+        }
+#pragma unroll
+        for (int t = 0; t < 9; ++t) {
+            const int kh = t / 3, kw = t - kh * 3;
+            if (!interior && ((unsigned)(iy0 + kh) >= (unsigned)h || (unsigned)(ix0 + kw) >= (unsigned)w)) continue;
+            unsigned u[4] = {v[t].x, v[t].y, v[t].z, v[t].w};
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const float lo = fmaxf(fmaf(bf16_lo(u[j]), sc[2 * j], sf[2 * j]), 0.f);
+                const float hi = fmaxf(fmaf(bf16_hi(u[j]), sc[2 * j + 1], sf[2 * j + 1]), 0.f);
+                u[j] = pack_bf16(lo, hi);
+            }
+            v[t] = make_uint4(u[0], u[1], u[2], u[3]);
+        }
     }
     const unsigned first = (unsigned)((iy0 < 0 ? 3 : 0) + (ix0 < 0 ? 1 : 0)) * 0x00010001u;
     __nv_bfloat162 m[4] = {as_bf162(ninf), as_bf162(ninf), as_bf162(ninf), as_bf162(ninf)};
@@ -226,7 +274,7 @@ maxpool_fwd_bf16_kernel(const __nv_bfloat16 *__restrict__ x, __nv_bfloat16 *__re
     }
     const unsigned nan = __hneu2_mask(m[0], m[0]) | __hneu2_mask(m[1], m[1]) | __hneu2_mask(m[2], m[2]) |
                          __hneu2_mask(m[3], m[3]);
-    if (nan == 0u) {
+    if (AFFINE || nan == 0u) {   // (after the ReLU there is no NaN: fmaxf maps it to 0)
         *reinterpret_cast<uint4 *>(y + (size_t)gid * 8) = make_uint4(as_u32(m[0]), as_u32(m[1]), as_u32(m[2]), as_u32(m[3]));
         *reinterpret_cast<uint2 *>(arg + (size_t)gid * 8) =
             make_uint2(__byte_perm(pos[0], pos[1], 0x6420), __byte_perm(pos[2], pos[3], 0x6420));
@@ -341,8 +389,8 @@ maxpool_bwd_bf16_kernel(const __nv_bfloat16 *__restrict__ dy, const __nv_bfloat1
 
 }  // namespace
 
-extern "C" int b200_maxpool3x3s2_fwd(const void *x, void *y, uint8_t *argmax, int64_t n, int c, int h, int w,
-                                     int dtype, void *stream) {
+static int maxpool_fwd_launch(const void *x, const float *scale_shift, void *y, uint8_t *argmax, int64_t n, int c,
+                              int h, int w, int dtype, void *stream) {
     if (!x || !y || !argmax || n < 1 || c < 8 || (c % 8) || h < 1 || w < 1) return (int)cudaErrorInvalidValue;
     if (dtype != B200_F32 && dtype != B200_BF16) return (int)cudaErrorInvalidValue;
     if (b200_misaligned(x) || b200_misaligned(y) || b200_misaligned(argmax, 8)) return (int)cudaErrorMisalignedAddress;
@@ -350,19 +398,39 @@ extern "C" int b200_maxpool3x3s2_fwd(const void *x, void *y, uint8_t *argmax, in
     const int64_t total = n * oh * ow * (c / 8);
     const unsigned blocks = (unsigned)((total + kThreads - 1) / kThreads);
     cudaStream_t st = static_cast<cudaStream_t>(stream);
-    if (dtype == B200_BF16 && total < (1ll << 31))
-        maxpool_fwd_bf16_kernel<<<blocks, kThreads, 0, st>>>(static_cast<const __nv_bfloat16 *>(x),
-                                                            static_cast<__nv_bfloat16 *>(y), argmax, (unsigned)total,
-                                                            make_fastdiv(c / 8), make_fastdiv(ow), make_fastdiv(oh), h, w);
-    else if (dtype == B200_BF16)
-        maxpool_fwd_kernel<__nv_bfloat16><<<blocks, kThreads, 0, st>>>(static_cast<const __nv_bfloat16 *>(x),
-                                                                      static_cast<__nv_bfloat16 *>(y), argmax, total,
-                                                                      c / 8, h, w, oh, ow);
-    else
-        maxpool_fwd_kernel<float><<<blocks, kThreads, 0, st>>>(static_cast<const float *>(x), static_cast<float *>(y),
-                                                              argmax, total, c / 8, h, w, oh, ow);
+    const bool fast = dtype == B200_BF16 && total < (1ll << 31);
+#define B200_POOL_FWD(AFFINE)                                                                                       \
+    do {                                                                                                            \
+        if (fast)                                                                                                   \
+            maxpool_fwd_bf16_kernel<AFFINE><<<blocks, kThreads, 0, st>>>(                                           \
+                static_cast<const __nv_bfloat16 *>(x), static_cast<__nv_bfloat16 *>(y), argmax, (unsigned)total,     \
+                make_fastdiv(c / 8), make_fastdiv(ow), make_fastdiv(oh), h, w, scale_shift);                        \
+        else if (dtype == B200_BF16)                                                                                \
+            maxpool_fwd_kernel<__nv_bfloat16, AFFINE><<<blocks, kThreads, 0, st>>>(                                 \
+                static_cast<const __nv_bfloat16 *>(x), static_cast<__nv_bfloat16 *>(y), argmax, total, c / 8, h, w, \
+                oh, ow, scale_shift);                                                                               \
+        else                                                                                                        \
+            maxpool_fwd_kernel<float, AFFINE><<<blocks, kThreads, 0, st>>>(                                         \
+                static_cast<const float *>(x), static_cast<float *>(y), argmax, total, c / 8, h, w, oh, ow,         \
+                scale_shift);                                                                                       \
+    } while (0)
+    if (scale_shift) B200_POOL_FWD(true);
+    else B200_POOL_FWD(false);
+#undef B200_POOL_FWD
     B200_CHECK_LAUNCH();
     return 0;
+}
+
+extern "C" int b200_maxpool3x3s2_fwd(const void *x, void *y, uint8_t *argmax, int64_t n, int c, int h, int w,
+                                     int dtype, void *stream) {
+    return maxpool_fwd_launch(x, nullptr, y, argmax, n, c, h, w, dtype, stream);
+}
+
+extern "C" int b200_bn_relu_maxpool3x3s2_fwd(const void *x, const float *scale_shift, void *y, uint8_t *argmax, int64_t n,
+                                             int c, int h, int w, int dtype, void *stream) {
+    if (!scale_shift) return (int)cudaErrorInvalidValue;
+    if (b200_misaligned(scale_shift, 4)) return (int)cudaErrorMisalignedAddress;
+    return maxpool_fwd_launch(x, scale_shift, y, argmax, n, c, h, w, dtype, stream);
 }
 
 extern "C" int b200_maxpool3x3s2_bwd(const void *dy, const void *dy2, const uint8_t *argmax, void *dx, int64_t n, int c,

@@ -352,6 +352,7 @@ class B200ResNet(nn.Module):
         self.register_load_state_dict_post_hook(lambda module, incompatible: module.weights_changed())
         self.__dict__["_sink"] = None  # data-parallel wrapper (grad_ready / backward_done); not a submodule
         self.grad_predivide = 1.0  # 1/world_size, set by the wrapper (DDP's pre-division)
+        self.fuse_stem_pool = True  # training forward: bn1 apply + ReLU + max-pool as one kernel (same bits)
 
     # ---- storage --------------------------------------------------------------------------------
     def _adopt(self, tv):
@@ -493,11 +494,19 @@ class B200ResNet(nn.Module):
         stem = self._stem(x)
         tape = {"x0": x, "stem": stem}
         t = stem.fwd(x)
-        a, saved, _ = self.bn1.fwd_train(t, _cabi.ACT_RELU)
+        bn = self.bn1
+        if self.fuse_stem_pool:
+            # statistics only; the apply + ReLU happens inside the pool kernel and relu(bn1(x)) is never materialised
+            # (the backward recomputes the ReLU mask from t and routes the pool's gradient through the argmax)
+            saved = _cabi.bn_stats(t, bn.weight, bn.bias, bn.running_mean, bn.running_var, bn.num_batches_tracked,
+                                   bn.eps, bn.momentum)
+            cur, idx = _cabi.bn_relu_maxpool_fwd(t, saved)
+        else:
+            a, saved, _ = bn.fwd_train(t, _cabi.ACT_RELU)
+            cur, idx = _cabi.maxpool_fwd(a)
+            del a
         tape["t1"], tape["saved1"] = t, saved
-        cur, idx = _cabi.maxpool_fwd(a)
-        tape["pool_idx"], tape["pool_in_shape"] = idx, a.shape
-        del a
+        tape["pool_idx"], tape["pool_in_shape"] = idx, t.shape
         tape["blocks"] = []
         for li in range(1, 5):
             for blk in getattr(self, f"layer{li}"):

@@ -271,6 +271,16 @@ int b200_maxpool3x3s2_fwd(const void *x, void *y, uint8_t *argmax, int64_t n, in
                           void *stream);
 int b200_maxpool3x3s2_bwd(const void *dy, const void *dy2, const uint8_t *argmax, void *dx, int64_t n, int c, int h,
                           int w, int dtype, void *stream);
+/* The stem's BatchNorm apply + ReLU + max-pool in one pass (torchvision resnet.py:269-270 then :200/:271:
+ * `x = self.bn1(x); x = self.relu(x); x = self.maxpool(x)`): every tap is mapped through
+ * relu(x*scale[ch] + shift[ch]) - float32 fma, rounded once to the activation dtype, i.e. exactly the values
+ * b200_bn_fwd_train(act = RELU) would have stored - before the comparison, so y and argmax are bit-identical to running
+ * the two kernels one after the other, while the normalised activation (4x the pooled one: 411 MB at N=256) is neither
+ * written nor read.  Nothing downstream needs it: the BatchNorm backward recomputes the ReLU mask from x, the pool's
+ * backward routes through argmax.  scale_shift: float32 [2,c] on the device = rows 2 and 3 of the `saved` tensor that
+ * b200_bn_stats / b200_bn_fwd_train write (saved + 2*c).  x: the convolution output [n,h,w,c]; y, argmax as above. */
+int b200_bn_relu_maxpool3x3s2_fwd(const void *x, const float *scale_shift, void *y, uint8_t *argmax, int64_t n, int c,
+                                  int h, int w, int dtype, void *stream);
 
 /* ------------------------------------------------------------------------------------------------
  * K4c  gradient exchange + optimizer step of one gradient bucket in ONE kernel over NVLink peer memory
@@ -286,8 +296,10 @@ int b200_maxpool3x3s2_bwd(const void *dy, const void *dy2, const uint8_t *argmax
  *   bucket   : 0..22, the same on every rank for the same [lo,hi) (element offsets, multiples of 4).
  *   max_ctas : CTAs the kernel may use (it runs beside the backward); <= 0 means 32.
  * Signal pads: b200_peer_pad_bytes() bytes per rank, zero before the first call, never touched by the host afterwards
- * except word 0, which a kernel sets to 1 if a peer's flag did not arrive within ~20 s (the kernel then carries on
- * instead of hanging the GPU; results of that step are garbage).  Every rank must launch the same buckets in the same
+ * except word 0, which a kernel sets to 1 if a peer's flag did not arrive within ~20 s.  The word latches: from then on
+ * this rank's kernels store nothing into any parameter / shadow / momentum arena, raise no completion flag and do not
+ * advance the iteration counter, so the peers time out in turn and stop updating too - replicas stay as they were
+ * before the failing iteration instead of being half-updated.  The host reads the word after a synchronise.  Every rank must launch the same buckets in the same
  * order each iteration and finish the iteration with b200_peer_wait, which waits until every rank's shard of every
  * bucket has arrived (and every peer has finished reading this rank's gradients) and advances the iteration counter.
  */

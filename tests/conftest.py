@@ -36,6 +36,6 @@ def cpu_kernels(monkeypatch):
     import imagent_distributed_training_pytorch_with_slurm_b200._cabi as cabi
 
     for name in ("bn_fwd_train", "bn_fwd_eval", "bn_bwd", "ce_topk_fwd", "ce_bwd", "sgd_flat", "input_stage", "maxpool_fwd",
-                 "maxpool_bwd", "pack_grads", "bn_dual_supported", "bn_stats", "bn_fwd_train_dual", "bn_bwd_dual"):
+                 "maxpool_bwd", "bn_relu_maxpool_fwd", "pack_grads", "bn_dual_supported", "bn_stats", "bn_fwd_train_dual", "bn_bwd_dual"):
         monkeypatch.setattr(cabi, name, getattr(s, name))
     return s

@@ -113,6 +113,12 @@ def maxpool_fwd(x):
     return torch.from_numpy(y).to(x.dtype).permute(0, 3, 1, 2), torch.from_numpy(pos)
 
 
+def bn_relu_maxpool_fwd(x, saved):
+    c = x.shape[1]
+    a = torch.relu(torch.addcmul(saved[3].view(1, c, 1, 1), x.float(), saved[2].view(1, c, 1, 1))).to(x.dtype)
+    return maxpool_fwd(a)
+
+
 def maxpool_bwd(dy, arg, in_shape, dy2=None):
     g = dy.permute(0, 2, 3, 1).float().numpy()
     if dy2 is not None:

@@ -26,7 +26,7 @@ def _worker(rank, world, port, gold, q):
         from oracle import train_cpu
         from tests import cpu_kernel_standins as s
 
-        for name in ("bn_fwd_train", "bn_fwd_eval", "bn_bwd", "ce_topk_fwd", "ce_bwd", "sgd_flat", "input_stage", "maxpool_fwd",
+        for name in ("bn_fwd_train", "bn_fwd_eval", "bn_bwd", "ce_topk_fwd", "ce_bwd", "sgd_flat", "input_stage", "maxpool_fwd", "bn_relu_maxpool_fwd",
                  "maxpool_bwd", "pack_grads", "bn_dual_supported", "bn_stats", "bn_fwd_train_dual", "bn_bwd_dual"):
             setattr(cabi, name, getattr(s, name))
         eng._to_device = lambda t: t

@@ -471,6 +471,31 @@ def test_maxpool_bf16_packed_path_follows_the_scalar_rule_with_nan_inf_and_signe
     assert torch.equal(ab.permute(0, 3, 1, 2).long(), pos)
 
 
+@pytest.mark.parametrize("shape", [(2, 9, 7, 8), (3, 12, 12, 64), (1, 5, 6, 16), (4, 56, 56, 64), (2, 1, 1, 8)])
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_stem_bn_relu_maxpool_in_one_pass_equals_the_two_kernels(shape, dtype):
+    """b200_bn_relu_maxpool3x3s2_fwd pools over relu(x*scale + shift) without storing it: values AND argmax must have the
+    bits of b200_bn_fwd_train(act=RELU) followed by b200_maxpool3x3s2_fwd (which are checked against the oracle above),
+    including windows cut by the image border and channels whose activations are all clipped to zero (ties)."""
+    n, h, w, c = shape
+    g = torch.Generator().manual_seed(h * 100 + w)
+    x = (torch.randn(n, h, w, c, generator=g) * 2.0 - 0.5).to(dtype).to(DEV).permute(0, 3, 1, 2)
+    gamma = torch.rand(c, generator=g).add(0.5).to(DEV)
+    beta = (torch.randn(c, generator=g) * 0.5).to(DEV)
+    beta[0] = -50.0                                           # a channel that the ReLU zeroes everywhere: all ties
+    if n * h * w < 2:
+        pytest.skip("training statistics need more than one value per channel")
+    rm, rv = torch.zeros(c, device=DEV), torch.ones(c, device=DEV)
+    a, saved, _ = cabi.bn_fwd_train(x, None, gamma, beta, rm, rv, None, 1e-5, 0.1, cabi.ACT_RELU)
+    y2, arg2 = cabi.maxpool_fwd(a)
+    rm2, rv2 = torch.zeros(c, device=DEV), torch.ones(c, device=DEV)
+    saved1 = cabi.bn_stats(x, gamma, beta, rm2, rv2, None, 1e-5, 0.1)
+    y1, arg1 = cabi.bn_relu_maxpool_fwd(x, saved1)
+    assert torch.equal(saved1, saved) and torch.equal(rm, rm2) and torch.equal(rv, rv2)
+    assert torch.equal(y1, y2) and torch.equal(arg1, arg2)
+    assert float(y1[:, 0].abs().max()) == 0.0 and int(arg1[..., 0].max()) <= 4   # ties resolve to the first tap inside
+
+
 def test_maxpool_full_size_against_aten():
     """BASELINE size [256,64,112,112] bf16: the library kernel the reference would have run is the
     checker here (max values and routed gradients must agree exactly / to one bf16 rounding)."""
