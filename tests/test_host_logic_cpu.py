@@ -142,3 +142,55 @@ def test_kernels_refuse_cpu_tensors():
     model = b200.build_model("resnet18", device="cpu", dtype=torch.float32)
     with pytest.raises(b200.B200Error):
         model(torch.randn(1, 3, 32, 32))
+
+
+def test_second_backward_without_zero_grad_or_step_raises(cpu_kernels):
+    """The backward overwrites the gradient arena where autograd would accumulate (the reference clears the gradients
+    before every backward, imagenet.py:127, and never accumulates): doing it twice must raise, not silently differ."""
+    torch.manual_seed(0)
+    model = b200.build_model("resnet18", device="cpu", dtype=torch.float32).train()
+    opt = b200.FlatSGD(model.parameters(), 0.01, momentum=0.9, weight_decay=1e-4)
+    g = torch.Generator().manual_seed(1)
+    x, t = torch.randn(2, 3, 32, 32, generator=g), torch.randint(0, 1000, (2,), generator=g)
+    crit = b200.CrossEntropyLoss()
+    crit(model(x), t).backward()
+    with pytest.raises(RuntimeError, match="does not accumulate"):
+        crit(model(x), t).backward()
+    opt.zero_grad()                      # re-arms
+    crit(model(x), t).backward()
+    opt.step()                           # so does step()
+    crit(model(x), t).backward()
+    model.zero_grad()                    # nn.Module.zero_grad must neither drop the permanent views nor break the guard
+    assert all(p.grad is not None for p in model.parameters())
+    crit(model(x), t).backward()
+
+
+def test_load_state_dict_refreshes_the_weights_the_convolutions_read(cpu_kernels):
+    """bf16 mode: convolutions read a bf16 shadow of the float32 arena; loading a checkpoint (bare or through the
+    data-parallel wrapper, imagenet.py:392's file) must bring it up to date."""
+    torch.manual_seed(0)
+    src = b200.build_model("resnet18", device="cpu", dtype=torch.bfloat16)
+    sd = b200.FlatDDP(src).state_dict()
+    torch.manual_seed(1)
+    dst = b200.FlatDDP(b200.build_model("resnet18", device="cpu", dtype=torch.bfloat16))
+    assert not torch.equal(dst.module.arena.shadow, src.arena.shadow)
+    dst.load_state_dict(sd)
+    assert torch.equal(dst.module.arena.params, src.arena.params)
+    assert torch.equal(dst.module.arena.shadow, src.arena.shadow)
+    assert torch.equal(dst.module.conv1.w_compute.float(), src.conv1.weight.detach().to(torch.bfloat16).float())
+    torch.manual_seed(2)
+    bare = b200.build_model("resnet18", device="cpu", dtype=torch.bfloat16)
+    bare.load_state_dict({k[len("module."):]: v for k, v in sd.items()})
+    assert torch.equal(bare.arena.shadow, src.arena.shadow)
+
+
+def test_meter_weight_is_the_reference_channel_count():
+    """imagenet.py:142: ``batch_size = input[0].size(0)`` is the CHANNEL count (3) of an NCHW batch; the 16-channel
+    stem layout must not change the weight the meters see."""
+    import imagent_distributed_training_pytorch_with_slurm_b200.engine as eng
+
+    x = torch.zeros(4, 3, 8, 8)
+    assert eng._meter_weight(x) == 3
+    s2d = torch.zeros(4, 16, 7, 7)
+    s2d._b200_s2d_stem = (8, 8)
+    assert eng._meter_weight(s2d) == 3
