@@ -102,15 +102,18 @@ def graph_level(rank, local, world):
     iterations, capture, replays), both with the per-iteration buffer broadcast from rank 0 (NCCL / peer copy)."""
     batches = [(x.cuda(), t.cuda()) for x, t in train_cpu.synthetic_batches(rank, 8, 16, 64, 1000, seed=77)]
     out = {}
-    for mode in ("nccl", "peer"):
+    # "peer_auto": the public switch, train(..., graph=True) - it must pick the single-graph runner for the peer path
+    # (the chain-of-graphs runner records NCCL all-reduces + a whole-arena SGD and would corrupt the rank-sharded momentum)
+    for mode in ("nccl", "peer", "peer_auto"):
+        exchange = "nccl" if mode == "nccl" else "peer"
         torch.manual_seed(5)
-        net = b200.build_model("resnet18", dtype=torch.bfloat16, symmetric=(mode == "peer")).cuda()
-        m = b200.FlatDDP(net, device_ids=[local], bucket_cap_mb=8, first_bucket_mb=1, exchange=mode)
+        net = b200.build_model("resnet18", dtype=torch.bfloat16, symmetric=(exchange == "peer")).cuda()
+        m = b200.FlatDDP(net, device_ids=[local], bucket_cap_mb=8, first_bucket_mb=1, exchange=exchange)
         o = b200.FlatSGD(m.parameters(), 0.002, momentum=0.9, weight_decay=1e-4)
         m.attach_optimizer(o)
-        runner = b200.GraphedStep(m, b200.CrossEntropyLoss().cuda(), o) if mode == "peer" else False
-        r = b200.train(batches, m, runner.criterion if runner else b200.CrossEntropyLoss().cuda(), o, 0, world,
-                       sync_every=1, lag=1, graph=runner)
+        runner = b200.GraphedStep(m, b200.CrossEntropyLoss().cuda(), o) if mode == "peer" else (mode == "peer_auto")
+        crit = runner.criterion if mode == "peer" else b200.CrossEntropyLoss().cuda()
+        r = b200.train(batches, m, crit, o, 0, world, sync_every=1, lag=1, graph=runner)
         torch.cuda.synchronize()
         sd = m.state_dict()
         out[mode] = {"epoch": list(map(float, r[:3])), "steps": m.module.arena.steps,
@@ -118,7 +121,12 @@ def graph_level(rank, local, world):
                      "w1": float(sd["module.conv1.weight"].double().norm()),
                      "rv": float(sd["module.bn1.running_var"].double().norm()),
                      "rv_all": _same_on_all_ranks(sd["module.layer4.1.bn2.running_var"]),
-                     "captured": bool(runner and runner.graph is not None), "error": bool(m.peer_error())}
+                     "captured": bool(mode == "peer" and runner.graph is not None), "error": bool(m.peer_error())}
+    try:   # and the chain-of-graphs runner must refuse the peer path outright
+        b200.SegmentedGraphStep(m, b200.CrossEntropyLoss().cuda(), o)
+        out["segmented_refuses_peer"] = False
+    except ValueError:
+        out["segmented_refuses_peer"] = True
     return out
 
 

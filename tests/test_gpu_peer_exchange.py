@@ -40,3 +40,9 @@ def test_two_gpu_peer_exchange_matches_closed_form_and_nccl_path():
     # BatchNorm buffers: rank 0's running statistics reach every rank through the peer copy, as through NCCL
     assert g["peer"]["rv"] == pytest.approx(g["nccl"]["rv"], rel=1e-3)
     assert g["peer"]["rv_all"] and g["nccl"]["rv_all"]
+    # train(..., graph=True) on the peer path: the public switch picks the single-graph runner and gives the same run
+    a = g["peer_auto"]
+    assert not a["error"] and a["steps"] == 8 and a["rv_all"]
+    assert a["epoch"][0] == pytest.approx(g["nccl"]["epoch"][0], rel=2e-3) and a["epoch"][1:] == g["nccl"]["epoch"][1:]
+    assert a["w"] == pytest.approx(g["nccl"]["w"], rel=1e-4) and a["rv"] == pytest.approx(g["nccl"]["rv"], rel=1e-3)
+    assert g["segmented_refuses_peer"]
