@@ -520,7 +520,7 @@ def run_ours(a):
     barrier()
     _cabi.stats.reset()
     _cabi.stats.timed = {"input", "bn_fwd", "bn_bwd", "ce_topk_fwd", "ce_bwd", "sgd", "maxpool_fwd", "maxpool_bwd",
-                         "pack"}
+                         "bn_relu_maxpool_fwd", "pack"}
     b0, b1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     b0.record()
     for i in range(a.warmup, total):
@@ -625,7 +625,7 @@ def run_ours(a):
                              "survey_8d_GB_per_step": n8d / a.steps / 1e9,
                              "GBps_survey_8d": n8d / 1e9 / (d["ms"] / 1e3) if d["ms"] > 0 else None}
         hbm = {k: v for k, v in kernels.items() if k in ("bn_fwd", "bn_bwd", "sgd", "input", "maxpool_fwd",
-                                                         "maxpool_bwd", "pack")}
+                                                         "maxpool_bwd", "bn_relu_maxpool_fwd", "pack")}
         dom = max(hbm, key=lambda k: hbm[k]["ms_per_step"]) if hbm else None
         roof = None
         if dom:

@@ -494,12 +494,12 @@ def bn_relu_maxpool_fwd(x, saved):
     oh, ow = (h - 1) // 2 + 1, (w - 1) // 2 + 1
     y = torch.empty((n, c, oh, ow), dtype=x.dtype, device=x.device, memory_format=torch.channels_last)
     arg = torch.empty((n, oh, ow, c), dtype=torch.uint8, device=x.device)
-    s = stats.begin("maxpool_fwd")
+    s = stats.begin("bn_relu_maxpool_fwd")
     _check(load().b200_bn_relu_maxpool3x3s2_fwd(_ptr(x), saved.data_ptr() + 2 * c * 4, _ptr(y), _ptr(arg), n, c, h, w,
                                                 dtype_code(x), _stream()), "b200_bn_relu_maxpool3x3s2_fwd")
     nbytes = x.numel() * x.element_size() + y.numel() * (x.element_size() + 1)
     # SURVEY 8d counts this work as the apply pass of a bn+relu site (2 E*s) plus the pool (x + y + argmax)
-    stats.end("maxpool_fwd", 1, s, nbytes, nbytes + 2 * x.numel() * x.element_size())
+    stats.end("bn_relu_maxpool_fwd", 1, s, nbytes, nbytes + 2 * x.numel() * x.element_size())
     return y, arg
 
 

@@ -154,7 +154,7 @@ PipeGeom make_geom_pipe(int64_t m, int c, int vec, int esize, int nt, bool mask,
     g.nchunk = (int)((m + rpc - 1) / rpc);
     const int per_sm = (g.nchunk + B200_SM_COUNT - 1) / B200_SM_COUNT;
     const size_t budget = (size_t)200 * 1024 / per_sm;
-    int st = (int)((budget > static_smem + 128 ? budget - static_smem - 128 : 0) / pipe_stage_bytes(nt, mask));
+    int st = (int)((budget > static_smem + kRingHeader ? budget - static_smem - kRingHeader : 0) / pipe_stage_bytes(nt, mask));
     if (st > kMaxStages) st = kMaxStages;
     if (st < 2) st = 2;
     if (g_bn_pipe_stages > 0) st = g_bn_pipe_stages;
@@ -237,7 +237,7 @@ FusedGeom make_geom_fused(int64_t m, int c, int vec, int esize, int nt1, bool ma
     const PipeGeom big = make_geom_pipe(m, c, vec, esize, first_larger ? nt1 : nt2, first_larger ? mask1 : mask2, static_smem);
     fg.g = big.g;
     fg.smem = big.smem;
-    const size_t data = big.smem - 128;
+    const size_t data = big.smem - kRingHeader;
     int s1 = (int)(data / pipe_stage_bytes(nt1, mask1)), s2 = (int)(data / pipe_stage_bytes(nt2, mask2));
     fg.stages1 = s1 > kMaxStages ? kMaxStages : s1;
     fg.stages2 = s2 > kMaxStages ? kMaxStages : s2;

@@ -120,13 +120,13 @@ bn_fwd_fused_kernel(const T *__restrict__ x, const T *__restrict__ z, T *__restr
             }
         }
     }
-    // pass 2's first tiles go in flight now (x and z do not depend on the statistics); second barrier set at byte 64
+    // pass 2's first tiles go in flight now (x and z do not depend on the statistics); second barrier set of the header
     TileRing<NT, false> ring;
     if (y) {
         ring.src[0] = reinterpret_cast<const unsigned char *>(x);
         if (NT == 2) ring.src[NT - 1] = reinterpret_cast<const unsigned char *>(z);
         ring.msrc = nullptr;
-        ring.setup(dyn_smem, txl, nstages2, (int64_t)c * sizeof(T), r0, r1, 64);
+        ring.setup(dyn_smem, txl, nstages2, (int64_t)c * sizeof(T), r0, r1, kRingHeader / 2);
     }
     __threadfence();
     grid.sync();
@@ -263,7 +263,7 @@ bn_bwd_fused_kernel(const T *__restrict__ dy, const T *__restrict__ dy2, const T
     }
     // pass 2 reads the same tensors again: restart the ring (second barrier set) so its first tiles are in flight
     // while the grid meets
-    ring.setup(dyn_smem, txl, nstages, (int64_t)c * sizeof(T), r0, r1, 64);
+    ring.setup(dyn_smem, txl, nstages, (int64_t)c * sizeof(T), r0, r1, kRingHeader / 2);
     __threadfence();
     grid.sync();
     {   // ---- fold (bn_bwd_finalize_kernel), channels dealt out over the CTAs

@@ -17,7 +17,8 @@
 // that the resident CTAs of an SM together keep ~200 KB in flight.
 #pragma once
 
-constexpr int kMaxStages = 8;
+constexpr int kMaxStages = 16;    // 16 x 8 KB per tensor: what ONE resident CTA per SM needs to keep ~128 KB in flight
+constexpr int kRingHeader = 256;  // two sets of kMaxStages mbarriers (8 bytes each)
 constexpr int kTileVecs = 512;
 constexpr int kPipeU = kTileVecs / kThreads;  // vectors per thread per tile
 
@@ -69,7 +70,7 @@ __device__ __forceinline__ void unpack16<__nv_bfloat16, 8>(const uint4 &t, float
 }
 
 constexpr size_t pipe_stage_bytes(int nt, bool mask) { return (size_t)nt * kTileVecs * 16 + (mask ? kTileVecs : 0); }
-constexpr size_t pipe_smem_bytes(int nt, bool mask, int stages) { return 128 + (size_t)stages * pipe_stage_bytes(nt, mask); }
+constexpr size_t pipe_smem_bytes(int nt, bool mask, int stages) { return kRingHeader + (size_t)stages * pipe_stage_bytes(nt, mask); }
 
 // The shared-memory ring.  All 256 threads call wait()/release(); thread 0 is the producer.
 template <int NT, bool MASK>
@@ -86,12 +87,12 @@ struct TileRing {
     }
     __device__ __forceinline__ unsigned char *mstage(int s) const { return msk + (size_t)s * kTileVecs; }
 
-    // bar_off: which of the two barrier sets of the 128-byte header to use (0 or 64) - a kernel that walks its rows
+    // bar_off: which of the two barrier sets of the header to use (0 or kRingHeader / 2) - a kernel that walks its rows
     // twice re-arms the ring on the second set instead of re-initialising barriers that may still be in use
     __device__ void setup(unsigned char *smem, int txl, int nstages, int64_t c_bytes, int64_t r0_, int64_t r1_,
                           int bar_off = 0) {
         bars = reinterpret_cast<uint64_t *>(smem + bar_off);
-        data = smem + 128;
+        data = smem + kRingHeader;
         stages = nstages;
         msk = data + (size_t)nstages * NT * kTileVecs * 16;
         cv = 1 << txl;

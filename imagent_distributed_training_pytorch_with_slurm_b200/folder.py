@@ -235,13 +235,24 @@ class ImageFolderLoader:
         batches = [ids[i:i + self.batch_size] for i in range(0, len(ids), self.batch_size)]
         q = queue.Queue(maxsize=self.prefetch)
         pool = ThreadPoolExecutor(self.workers)
+        stop = threading.Event()
+
+        def put(item):
+            while not stop.is_set():       # a consumer that stopped early must not leave this thread blocked forever
+                try:
+                    q.put(item, timeout=0.2)
+                    return True
+                except queue.Full:
+                    pass
+            return False
 
         def produce():
             try:
                 for b in batches:
-                    q.put(self._host_batch(pool, b))
+                    if not put(self._host_batch(pool, b)):
+                        return
             except BaseException as e:  # noqa: BLE001  (surface it in the consumer)
-                q.put(e)
+                put(e)
 
         threading.Thread(target=produce, daemon=True).start()
         try:
@@ -251,4 +262,5 @@ class ImageFolderLoader:
                     raise item
                 yield self._stage(item)
         finally:
+            stop.set()
             pool.shutdown(wait=False, cancel_futures=True)

@@ -50,7 +50,7 @@ const char *b200_error_string(int code);
  *                      dependent launch (they start while their predecessor drains), default 1
  *   "bn_fused"         1 = one cooperative kernel per BatchNorm site (statistics, fold and apply with grid-wide barriers
  *                      inside) instead of the three-kernel chain; same bits, measured slower on B200, default 0
- *   "bn_pipe_stages"   shared-memory ring depth of the bulk-async kernels, 2..8 (default 0 = automatic)
+ *   "bn_pipe_stages"   shared-memory ring depth of the bulk-async kernels, 2..16 (default 0 = automatic)
  *   "input_s2d_fast"   1 (default): B200_LAYOUT_S2D_STEM output is produced by the cell-per-thread kernel;
  *                      0: by the generic kernel (same bits, slower; kept as the in-library cross-check)
  * Returns cudaErrorInvalidValue for an unknown key or value. */
