@@ -1,9 +1,10 @@
 """Summarise an ncu launch list (`ncu --metrics gpu__time_duration.sum,dram__bytes_read.sum,dram__bytes_write.sum
 --clock-control none --csv --log-file X.csv python bench.py --steps 2 --warmup 2 --no-cpu-baseline --no-e2e --no-graph`).
 
-Writes, next to this script: r01_launch_summary.txt (per-kernel totals of the LAST step = region B of bench.py),
-r01_launches_last_step.csv (one row per launch) and traffic.json (mean DRAM bytes per BatchNorm call, read by bench.py).
-Steps are delimited by the input-stage coefficient kernel.  Usage: python summarize_launches.py X.csv"""
+Writes, next to this script: <round>_launch_summary.txt (per-kernel totals of the LAST step = region B of bench.py),
+<round>_launches_last_step.csv (one row per launch) and traffic.json (mean DRAM bytes per BatchNorm call, read by
+bench.py).  Steps are delimited by the input-stage coefficient kernel.
+Usage: python summarize_launches.py X.csv [round, default r02]"""
 import collections
 import csv
 import json
@@ -26,7 +27,7 @@ def short(n):
     return base[-64:]
 
 
-def main(path):
+def main(path, rnd="r02"):
     with open(path) as f:
         lines = [l for l in f if not l.startswith("==")]
     launches = collections.OrderedDict()
@@ -52,7 +53,7 @@ def main(path):
            f"{tot / 1e6:.3f} ms summed kernel time (cold cache, serialised)",
            f"owned kernels: {sum(d[T] for d in own) / 1e6:.3f} ms = {100 * sum(d[T] for d in own) / tot:.1f} % of the "
            f"summed kernel time"]
-    fam = {"bn_fwd": ("bn_stats", "bn_fwd_finalize", "bn_apply"), "bn_bwd": ("bn_bwd_",)}
+    fam = {"bn_fwd": ("bn_stats", "bn_fwd_finalize", "bn_apply"), "bn_bwd": ("bn_bwd_",)}   # (calls = finalize launches)
     traffic = {}
     for name, pre in fam.items():
         sel = [d for d in own if any(p in d["kernel"] for p in pre)]
@@ -71,8 +72,8 @@ def main(path):
         a[2] += d.get(R, 0) + d.get(W, 0)
     for k, (c, t, b) in sorted(agg.items(), key=lambda kv: -kv[1][1])[:48]:
         out.append(f"{t / 1e6:7.3f} ms {100 * t / tot:5.1f}%  x{c:3d}  {b / 1e9:8.2f} GB  {b / t / 1e3 if t else 0:5.2f} TB/s  {k}")
-    open(os.path.join(HERE, "r01_launch_summary.txt"), "w").write("\n".join(out) + "\n")
-    with open(os.path.join(HERE, "r01_launches_last_step.csv"), "w", newline="") as f:
+    open(os.path.join(HERE, f"{rnd}_launch_summary.txt"), "w").write("\n".join(out) + "\n")
+    with open(os.path.join(HERE, f"{rnd}_launches_last_step.csv"), "w", newline="") as f:
         w = csv.writer(f)
         w.writerow(["id", "kernel", "grid", "block", "time_ns", "dram_read_MB", "dram_write_MB"])
         for d in last:
@@ -80,10 +81,10 @@ def main(path):
                         round(d.get(W, 0) / 1e6, 3)])
     traffic["unit"] = ("DRAM bytes (read+write) per BatchNorm call (its 2-3 launches), mean over the sites of one "
                        "ResNet-50 step, N=256 bf16")
-    traffic["source"] = "profiles/r01_launches_last_step.csv (ncu dram__bytes_read.sum + dram__bytes_write.sum)"
+    traffic["source"] = f"profiles/{rnd}_launches_last_step.csv (ncu dram__bytes_read.sum + dram__bytes_write.sum)"
     json.dump(traffic, open(os.path.join(HERE, "traffic.json"), "w"), indent=1)
     print("\n".join(out[:12]))
 
 
 if __name__ == "__main__":
-    main(sys.argv[1])
+    main(*sys.argv[1:3])
