@@ -59,6 +59,42 @@ def _rendezvous():
     return n_nodes, node_id, local_rank, global_rank, world_size
 
 
+def make_loaders(args, world_size, global_rank, dtype):
+    """Datasets, samplers and loaders as run() builds them (imagenet.py:280-296,346-359).  Returns
+    (train_loader, val_loader, train_sampler, val_sampler, num_classes, n_train, n_val)."""
+    if not args.synthetic and not args.data:
+        # the reference's hard-wired location (imagenet.py:285-289): ../data/imagenet relative to the working directory
+        args.data = os.path.join(os.path.abspath(os.path.join(".", os.pardir)), "data/imagenet")
+    ref_mode = not args.random_crop
+    mean, std = (b200_data.REFERENCE_MEAN, b200_data.REFERENCE_STD) if ref_mode else \
+        (b200_data.IMAGENET_MEAN, b200_data.IMAGENET_STD)
+    if args.synthetic:
+        # a virtual dataset of --synthetic images (validation: 1/25 of that), walked in DistributedSampler order
+        num_classes = 1000
+        n_train, n_val = args.synthetic, max(1, args.synthetic // 25)
+        train_sampler = DistributedSampler(n_train, num_replicas=world_size, rank=global_rank)
+        val_sampler = DistributedSampler(n_val, num_replicas=world_size, rank=global_rank)
+        common = dict(src_size=args.source_size, out_size=args.image_size, num_classes=num_classes, rank=global_rank,
+                      mean=mean, std=std, dtype=dtype, host=True)
+        train_loader = b200_data.SyntheticImageNet(args.batch_size, 0, random_crop=not ref_mode, sampler=train_sampler,
+                                                   **common)
+        val_loader = b200_data.SyntheticImageNet(args.batch_size, 0, random_crop=False, seed=4321, sampler=val_sampler,
+                                                 **common)
+    else:
+        # datasets.ImageNet(root, split) x2, DistributedSampler x2, DataLoader x2 (imagenet.py:293-296,346-359)
+        trainset = ImageFolderIndex(args.data, "train")
+        valset = ImageFolderIndex(args.data, "val")
+        num_classes = len(trainset.classes)
+        n_train, n_val = len(trainset), len(valset)
+        train_sampler = DistributedSampler(trainset, num_replicas=world_size, rank=global_rank)
+        val_sampler = DistributedSampler(valset, num_replicas=world_size, rank=global_rank)
+        common = dict(out_size=args.image_size, mean=mean, std=std, dtype=dtype, decoder=args.decoder,
+                      workers=args.workers, rank=global_rank)
+        train_loader = ImageFolderLoader(trainset, train_sampler, args.batch_size, random_crop=not ref_mode, **common)
+        val_loader = ImageFolderLoader(valset, val_sampler, args.batch_size, random_crop=False, **common)
+    return train_loader, val_loader, train_sampler, val_sampler, num_classes, n_train, n_val
+
+
 def run(args):
     torch.manual_seed(args.seed)
     n_nodes, node_id, local_rank, global_rank, world_size = _rendezvous()
@@ -85,37 +121,9 @@ def run(args):
     print(f"Backend: {dist.get_backend()}")
 
     print("Initialize Dataloaders...")
-    if not args.synthetic and not args.data:
-        # the reference's hard-wired location (imagenet.py:285-289): ../data/imagenet relative to the working directory
-        args.data = os.path.join(os.path.abspath(os.path.join(".", os.pardir)), "data/imagenet")
-    ref_mode = not args.random_crop
-    mean, std = (b200_data.REFERENCE_MEAN, b200_data.REFERENCE_STD) if ref_mode else \
-        (b200_data.IMAGENET_MEAN, b200_data.IMAGENET_STD)
     dtype = torch.bfloat16 if args.bf16 else torch.float32      # the reference trains in float32 (no autocast anywhere)
-    if args.synthetic:
-        # a virtual dataset of --synthetic images (validation: 1/25 of that), walked in DistributedSampler order
-        num_classes = 1000
-        n_train, n_val = args.synthetic, max(1, args.synthetic // 25)
-        train_sampler = DistributedSampler(n_train, num_replicas=world_size, rank=global_rank)
-        val_sampler = DistributedSampler(n_val, num_replicas=world_size, rank=global_rank)
-        common = dict(src_size=args.source_size, out_size=args.image_size, num_classes=num_classes, rank=global_rank,
-                      mean=mean, std=std, dtype=dtype, host=True)
-        train_loader = b200_data.SyntheticImageNet(args.batch_size, 0, random_crop=not ref_mode, sampler=train_sampler,
-                                                   **common)
-        val_loader = b200_data.SyntheticImageNet(args.batch_size, 0, random_crop=False, seed=4321, sampler=val_sampler,
-                                                 **common)
-    else:
-        # datasets.ImageNet(root, split) x2, DistributedSampler x2, DataLoader x2 (imagenet.py:293-296,346-359)
-        trainset = ImageFolderIndex(args.data, "train")
-        valset = ImageFolderIndex(args.data, "val")
-        num_classes = len(trainset.classes)
-        n_train, n_val = len(trainset), len(valset)
-        train_sampler = DistributedSampler(trainset, num_replicas=world_size, rank=global_rank)
-        val_sampler = DistributedSampler(valset, num_replicas=world_size, rank=global_rank)
-        common = dict(out_size=args.image_size, mean=mean, std=std, dtype=dtype, decoder=args.decoder,
-                      workers=args.workers, rank=global_rank)
-        train_loader = ImageFolderLoader(trainset, train_sampler, args.batch_size, random_crop=not ref_mode, **common)
-        val_loader = ImageFolderLoader(valset, val_sampler, args.batch_size, random_crop=False, **common)
+    train_loader, val_loader, train_sampler, val_sampler, num_classes, n_train, n_val = make_loaders(
+        args, world_size, global_rank, dtype)
     print("Training samples: {} images ".format(n_train))
     print("Test samples: {} images ".format(n_val))
     print("number of classes: {}".format(num_classes))

@@ -166,3 +166,36 @@ def test_cli_trains_from_a_dataset_folder(tmp_path, decoder):
     for line in ("Training samples: 15 images ", "Test samples: 6 images ", "number of classes: 3", "Epoch 2 Summary: ",
                  "Training Summary:"):
         assert line in r.stdout, (line, r.stdout[-1500:])
+
+
+@pytest.mark.parametrize("world,rank", [(1, 0), (4, 3)])
+def test_cli_loaders_walk_the_sampler_in_both_modes(tmp_path, world, rank):
+    """The loaders exactly as the command line builds them (imagenet.make_loaders = the data part of run()): with a
+    dataset folder and with --synthetic, an epoch must serve this rank's DistributedSampler indices of THAT epoch -
+    checked against the oracle sampler, which the goldens pin bit-exact on torch's (imagenet.py:346-347,375)."""
+    from imagent_distributed_training_pytorch_with_slurm_b200 import imagenet as cli
+
+    data = make_dataset(str(tmp_path / "data"))
+    # --data: targets served == class of the sampler's indices, per epoch
+    args = cli.build_parser().parse_args(["--data", data, "--batch-size", "4", "--image-size", "32", "--workers", "2"])
+    tl, vl, ts, vs, ncls, n_train, n_val = cli.make_loaders(args, world, rank, torch.float32)
+    assert (ncls, n_train, n_val) == (3, 15, 6)
+    for epoch in (0, 1, 5):
+        ts.set_epoch(epoch)
+        want = osamp.sampler_indices_oracle(n_train, world, rank, epoch).tolist()
+        got = torch.cat([t for _, t in tl]).tolist()
+        assert got == [tl.index.samples[i][1] for i in want]
+    want_val = osamp.sampler_indices_oracle(n_val, world, rank, 0).tolist()          # the reference never moves it
+    assert torch.cat([t for _, t in vl]).tolist() == [vl.index.samples[i][1] for i in want_val]
+    # --synthetic N: label of virtual image i is i % classes, so the targets reveal the index stream
+    args = cli.build_parser().parse_args(["--synthetic", "1003", "--batch-size", "64", "--image-size", "32",
+                                          "--source-size", "40"])
+    tl, vl, ts, vs, ncls, n_train, n_val = cli.make_loaders(args, world, rank, torch.bfloat16)
+    assert (ncls, n_train, n_val) == (1000, 1003, 40) and len(tl) == -(-len(ts) // 64)
+    for epoch in (0, 2):
+        ts.set_epoch(epoch)
+        want = osamp.sampler_indices_oracle(1003, world, rank, epoch)
+        batches = [(x.shape[0], t) for x, t in tl]
+        got = torch.cat([t for _, t in batches]).cpu()
+        assert torch.equal(got, torch.from_numpy(want) % 1000)
+        assert [n for n, _ in batches][-1] == len(want) - 64 * (len(batches) - 1)      # short last batch, no drop_last
