@@ -853,6 +853,7 @@ int check_common(int64_t m, int c, int act, int dtype, int vec) {
 extern "C" int b200_bn_vec(int dtype) { return dtype == B200_BF16 ? g_bn_vec_bf16 : 4; }
 
 extern int g_input_s2d_fast;  // input.cu
+extern int g_pack_steps;      // pack.cu
 
 extern "C" int b200_tune_set(const char *key, int value) {
     if (!key) return (int)cudaErrorInvalidValue;
@@ -865,6 +866,7 @@ extern "C" int b200_tune_set(const char *key, int value) {
     if (eq("bn_pdl")) { g_bn_pdl = value != 0; return 0; }
     if (eq("bn_fused")) { g_bn_fused = value != 0; return 0; }
     if (eq("input_s2d_fast")) { g_input_s2d_fast = value != 0; return 0; }
+    if (eq("pack_steps")) { if (value != 4 && value != 8) return (int)cudaErrorInvalidValue; g_pack_steps = value; return 0; }
     if (eq("bn_pipe_stages")) { if (value < 0 || value > kMaxStages || value == 1) return (int)cudaErrorInvalidValue; g_bn_pipe_stages = value; return 0; }
     if (eq("bn_pipe_ctas_per_sm")) { if (value < 1 || value > 8) return (int)cudaErrorInvalidValue; g_bn_pipe_ctas_per_sm = value; return 0; }
     return (int)cudaErrorInvalidValue;

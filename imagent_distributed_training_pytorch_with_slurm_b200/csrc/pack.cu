@@ -11,7 +11,8 @@ namespace {
 constexpr int kThreads = 256;
 constexpr int kMaxTensors = 64;
 
-constexpr int kBlockElems = kThreads * 8 * 4;   // elements one CTA converts: 4 steps of 8 per thread (16 KB in, 32 KB out)
+// elements one CTA converts: STEPS vectors of 8 per thread (STEPS = 4: 16 KB in, 32 KB out)
+constexpr int block_elems(int steps) { return kThreads * 8 * steps; }
 
 struct PackTable {
     const void *src[kMaxTensors];
@@ -23,9 +24,10 @@ struct PackTable {
 // The first version gave every tensor the same 32 CTAs: the 9.4 MB tensors of layer4 set the duration while the CTAs
 // of the small ones idled (3.5 TB/s).  Now the grid is flat over all tensors' 8192-element blocks and a CTA finds its
 // tensor by binary search in the prefix table (kernel parameter space = constant bank, uniform across the CTA).
-template <typename T>
+template <typename T, int STEPS>
 __global__ void __launch_bounds__(kThreads) pack_grads_kernel(const __grid_constant__ PackTable tab, int n_tensors,
                                                               float *__restrict__ dst, float scale) {
+    constexpr int kBlockElems = block_elems(STEPS);
     int lo = 0, hi = n_tensors;   // largest t with first_block[t] <= blockIdx.x
     while (hi - lo > 1) {
         const int mid = (lo + hi) >> 1;
@@ -37,7 +39,7 @@ __global__ void __launch_bounds__(kThreads) pack_grads_kernel(const __grid_const
     const long long n = tab.cnt[t];
     const long long n8 = n >> 3;
     const long long v0 = (long long)((int)blockIdx.x - tab.first_block[t]) * (kBlockElems / 8);
-    constexpr int kSteps = kBlockElems / 8 / kThreads;
+    constexpr int kSteps = STEPS;
     // all of a thread's loads are issued before its first store (the sources are dead after this kernel: streaming
     // loads; the arena is read next by the all-reduce / the optimizer: ordinary stores, it stays in L2)
     float e[kSteps][8];
@@ -77,11 +79,15 @@ __global__ void __launch_bounds__(kThreads) pack_grads_kernel(const __grid_const
 
 }  // namespace
 
+int g_pack_steps = 4;   // b200_tune_set("pack_steps", 4 | 8): vectors per thread
+
 extern "C" int b200_pack_grads(const void *const *srcs, const int64_t *offsets, const int64_t *counts, int n_tensors,
                                float *dst, float scale, int src_dtype, void *stream) {
     if (n_tensors < 0 || (n_tensors > 0 && (!srcs || !offsets || !counts || !dst))) return (int)cudaErrorInvalidValue;
     if (src_dtype != B200_F32 && src_dtype != B200_BF16) return (int)cudaErrorInvalidValue;
     cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const int steps = g_pack_steps == 8 ? 8 : 4;
+    const int kBlockElems = block_elems(steps);
     for (int base = 0; base < n_tensors; base += kMaxTensors) {
         const int m = n_tensors - base < kMaxTensors ? n_tensors - base : kMaxTensors;
         PackTable tab;
@@ -100,10 +106,14 @@ extern "C" int b200_pack_grads(const void *const *srcs, const int64_t *offsets, 
         for (int i = m; i < kMaxTensors; ++i) { tab.src[i] = nullptr; tab.off[i] = 0; tab.cnt[i] = 0; }
         for (int i = m; i <= kMaxTensors; ++i) tab.first_block[i] = (int)blocks;
         if (b200_misaligned(dst)) return (int)cudaErrorMisalignedAddress;
-        if (src_dtype == B200_BF16)
-            pack_grads_kernel<__nv_bfloat16><<<(unsigned)blocks, kThreads, 0, st>>>(tab, m, dst, scale);
+        if (src_dtype == B200_BF16 && steps == 8)
+            pack_grads_kernel<__nv_bfloat16, 8><<<(unsigned)blocks, kThreads, 0, st>>>(tab, m, dst, scale);
+        else if (src_dtype == B200_BF16)
+            pack_grads_kernel<__nv_bfloat16, 4><<<(unsigned)blocks, kThreads, 0, st>>>(tab, m, dst, scale);
+        else if (steps == 8)
+            pack_grads_kernel<float, 8><<<(unsigned)blocks, kThreads, 0, st>>>(tab, m, dst, scale);
         else
-            pack_grads_kernel<float><<<(unsigned)blocks, kThreads, 0, st>>>(tab, m, dst, scale);
+            pack_grads_kernel<float, 4><<<(unsigned)blocks, kThreads, 0, st>>>(tab, m, dst, scale);
         B200_CHECK_LAUNCH();
     }
     return 0;
