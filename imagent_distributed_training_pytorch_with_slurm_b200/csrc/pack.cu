@@ -27,7 +27,7 @@ struct PackTable {
 template <typename T, int STEPS>
 __global__ void __launch_bounds__(kThreads) pack_grads_kernel(const __grid_constant__ PackTable tab, int n_tensors,
                                                               float *__restrict__ dst, float scale) {
-    constexpr int kBlockElems = block_elems(STEPS);
+    constexpr int kBlockElems = kThreads * 8 * STEPS;
     int lo = 0, hi = n_tensors;   // largest t with first_block[t] <= blockIdx.x
     while (hi - lo > 1) {
         const int mid = (lo + hi) >> 1;
