@@ -866,7 +866,7 @@ extern "C" int b200_tune_set(const char *key, int value) {
     if (eq("bn_pdl")) { g_bn_pdl = value != 0; return 0; }
     if (eq("bn_fused")) { g_bn_fused = value != 0; return 0; }
     if (eq("input_s2d_fast")) { g_input_s2d_fast = value != 0; return 0; }
-    if (eq("pack_steps")) { if (value != 4 && value != 8) return (int)cudaErrorInvalidValue; g_pack_steps = value; return 0; }
+    if (eq("pack_steps")) { if (value != 1 && value != 2 && value != 4 && value != 8) return (int)cudaErrorInvalidValue; g_pack_steps = value; return 0; }
     if (eq("bn_pipe_stages")) { if (value < 0 || value > kMaxStages || value == 1) return (int)cudaErrorInvalidValue; g_bn_pipe_stages = value; return 0; }
     if (eq("bn_pipe_ctas_per_sm")) { if (value < 1 || value > 8) return (int)cudaErrorInvalidValue; g_bn_pipe_ctas_per_sm = value; return 0; }
     return (int)cudaErrorInvalidValue;

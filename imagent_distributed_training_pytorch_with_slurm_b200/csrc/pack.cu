@@ -79,14 +79,17 @@ __global__ void __launch_bounds__(kThreads) pack_grads_kernel(const __grid_const
 
 }  // namespace
 
-int g_pack_steps = 4;   // b200_tune_set("pack_steps", 4 | 8): vectors per thread
+// b200_tune_set("pack_steps", 1 | 2 | 4 | 8): 16-byte vectors per thread.  Measured on B200 (tools/probe_pack.py, ResNet-50's
+// 53 weight gradients = 141 MB moved, L2 flushed): 28.7 / 30.7 / 32.8 / 36.9 us = 4.9 / 4.6 / 4.3 / 3.8 TB/s - with 53 ragged
+// tensors the small blocks fill the tail of the launch better than deep per-thread batching helps.
+int g_pack_steps = 1;
 
 extern "C" int b200_pack_grads(const void *const *srcs, const int64_t *offsets, const int64_t *counts, int n_tensors,
                                float *dst, float scale, int src_dtype, void *stream) {
     if (n_tensors < 0 || (n_tensors > 0 && (!srcs || !offsets || !counts || !dst))) return (int)cudaErrorInvalidValue;
     if (src_dtype != B200_F32 && src_dtype != B200_BF16) return (int)cudaErrorInvalidValue;
     cudaStream_t st = static_cast<cudaStream_t>(stream);
-    const int steps = g_pack_steps == 8 ? 8 : 4;
+    const int steps = (g_pack_steps == 8 || g_pack_steps == 4 || g_pack_steps == 2) ? g_pack_steps : 1;
     const int kBlockElems = block_elems(steps);
     for (int base = 0; base < n_tensors; base += kMaxTensors) {
         const int m = n_tensors - base < kMaxTensors ? n_tensors - base : kMaxTensors;
@@ -106,14 +109,18 @@ extern "C" int b200_pack_grads(const void *const *srcs, const int64_t *offsets, 
         for (int i = m; i < kMaxTensors; ++i) { tab.src[i] = nullptr; tab.off[i] = 0; tab.cnt[i] = 0; }
         for (int i = m; i <= kMaxTensors; ++i) tab.first_block[i] = (int)blocks;
         if (b200_misaligned(dst)) return (int)cudaErrorMisalignedAddress;
-        if (src_dtype == B200_BF16 && steps == 8)
-            pack_grads_kernel<__nv_bfloat16, 8><<<(unsigned)blocks, kThreads, 0, st>>>(tab, m, dst, scale);
-        else if (src_dtype == B200_BF16)
-            pack_grads_kernel<__nv_bfloat16, 4><<<(unsigned)blocks, kThreads, 0, st>>>(tab, m, dst, scale);
-        else if (steps == 8)
-            pack_grads_kernel<float, 8><<<(unsigned)blocks, kThreads, 0, st>>>(tab, m, dst, scale);
-        else
-            pack_grads_kernel<float, 4><<<(unsigned)blocks, kThreads, 0, st>>>(tab, m, dst, scale);
+#define B200_PACK(T, S) pack_grads_kernel<T, S><<<(unsigned)blocks, kThreads, 0, st>>>(tab, m, dst, scale)
+#define B200_PACK_T(T)                                                                                             \
+    do {                                                                                                           \
+        if (steps == 8) B200_PACK(T, 8);                                                                           \
+        else if (steps == 4) B200_PACK(T, 4);                                                                      \
+        else if (steps == 2) B200_PACK(T, 2);                                                                      \
+        else B200_PACK(T, 1);                                                                                      \
+    } while (0)
+        if (src_dtype == B200_BF16) B200_PACK_T(__nv_bfloat16);
+        else B200_PACK_T(float);
+#undef B200_PACK_T
+#undef B200_PACK
         B200_CHECK_LAUNCH();
     }
     return 0;

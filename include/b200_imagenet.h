@@ -53,7 +53,7 @@ const char *b200_error_string(int code);
  *   "bn_pipe_stages"   shared-memory ring depth of the bulk-async kernels, 2..16 (default 0 = automatic)
  *   "input_s2d_fast"   1 (default): B200_LAYOUT_S2D_STEM output is produced by the cell-per-thread kernel;
  *                      0: by the generic kernel (same bits, slower; kept as the in-library cross-check)
- *   "pack_steps"       16-byte vectors per thread of the gradient pack kernel, 4 (default) or 8
+ *   "pack_steps"       16-byte vectors per thread of the gradient pack kernel: 1 (default), 2, 4 or 8
  * Returns cudaErrorInvalidValue for an unknown key or value. */
 int b200_tune_set(const char *key, int value);
 

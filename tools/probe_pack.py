@@ -20,7 +20,7 @@ for i, shp in enumerate(a.shapes):
         srcs.append(torch.randn(shp, device=dev).to(torch.bfloat16).contiguous(memory_format=torch.channels_last))
         offs.append(a.offsets[i])
 nbytes = sum(t.numel() * 6 for t in srcs)
-for steps in (4, 8, 4, 8):
+for steps in (1, 2, 4, 8, 1, 2, 4):
     cabi.tune_set("pack_steps", steps)
     ts = []
     for _ in range(15):
@@ -34,4 +34,4 @@ for steps in (4, 8, 4, 8):
     ts.sort()
     t = ts[len(ts) // 2]
     print(json.dumps({"pack_steps": steps, "us": round(t, 1), "MB": round(nbytes / 1e6, 1), "GBps": round(nbytes / t / 1e3)}))
-cabi.tune_set("pack_steps", 4)
+cabi.tune_set("pack_steps", 1)
