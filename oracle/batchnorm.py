@@ -59,3 +59,55 @@ def bn_train_bwd_oracle(dy, x, gamma, mean, invstd, act=ACT_NONE, relu_mask=None
     f = np.float32
     dz = dy64.astype(f) if act == ACT_ADD_RELU else None
     return dx.astype(f), dz, dgamma.astype(f), dbeta.astype(f)
+
+
+def bn_fwd_bwd_chunked_oracle(x, gamma, beta, dy, act=ACT_NONE, z=None, dy2=None, eps=1e-5, chunk_rows=65536):
+    """The same arithmetic as ``bn_train_fwd_oracle`` + ``bn_train_bwd_oracle`` for activations too large to hold in
+    float64 at once (a BASELINE-size site is 802,816 x 256): every pass walks ``chunk_rows`` rows at a time, all sums
+    are float64.  ``dy2``: second gradient branch (the residual fan-in autograd would add first).  Returns a dict with
+    mean, invstd (float64), y, dx, dz (float32, dz None unless add+relu), dgamma, dbeta (float64)."""
+    m, c = x.shape
+    g64, b64 = np.asarray(gamma, np.float64), np.asarray(beta, np.float64)
+    chunks = [(r, min(r + chunk_rows, m)) for r in range(0, m, chunk_rows)]
+    s1 = np.zeros(c)
+    for r0, r1 in chunks:
+        s1 += np.asarray(x[r0:r1], np.float64).sum(axis=0)
+    mean = s1 / m
+    s2 = np.zeros(c)
+    for r0, r1 in chunks:
+        d = np.asarray(x[r0:r1], np.float64) - mean
+        s2 += (d * d).sum(axis=0)
+    var = s2 / m
+    invstd = 1.0 / np.sqrt(var + eps)
+    y = np.empty((m, c), np.float32)
+    dbeta, dgamma = np.zeros(c), np.zeros(c)
+    for r0, r1 in chunks:
+        xhat = (np.asarray(x[r0:r1], np.float64) - mean) * invstd
+        v = xhat * g64 + b64
+        if act == ACT_ADD_RELU:
+            v = v + np.asarray(z[r0:r1], np.float64)
+        y[r0:r1] = np.maximum(v, 0.0) if act != ACT_NONE else v
+        g = np.asarray(dy[r0:r1], np.float64)
+        if dy2 is not None:
+            g = g + np.asarray(dy2[r0:r1], np.float64)
+        if act != ACT_NONE:
+            g = g * (v > 0)
+        dbeta += g.sum(axis=0)
+        dgamma += (g * xhat).sum(axis=0)
+    dx = np.empty((m, c), np.float32)
+    dz = np.empty((m, c), np.float32) if act == ACT_ADD_RELU else None
+    for r0, r1 in chunks:
+        xhat = (np.asarray(x[r0:r1], np.float64) - mean) * invstd
+        g = np.asarray(dy[r0:r1], np.float64)
+        if dy2 is not None:
+            g = g + np.asarray(dy2[r0:r1], np.float64)
+        if act != ACT_NONE:
+            v = xhat * g64 + b64
+            if act == ACT_ADD_RELU:
+                v = v + np.asarray(z[r0:r1], np.float64)
+            g = g * (v > 0)
+        dx[r0:r1] = g64 * invstd * (g - dbeta / m - xhat * dgamma / m)
+        if dz is not None:
+            dz[r0:r1] = g
+    return {"mean": mean, "invstd": invstd, "var_unbiased": var * (m / max(m - 1, 1)), "y": y, "dx": dx, "dz": dz,
+            "dgamma": dgamma, "dbeta": dbeta}

@@ -281,6 +281,51 @@ def test_bn_single_kernel_form_is_bit_identical_to_the_three_kernel_chain(m, c, 
         assert torch.equal(a, b), i
 
 
+def test_bn_baseline_size_add_relu_with_fan_in_matches_the_chunked_float64_oracle():
+    """One BASELINE-size bn+add+relu site (ResNet-50 layer1, N=256: [256,256,56,56] = 802,816 x 256, bf16) - the path
+    that carries most of the step's bytes - against the oracle itself, not only its properties: forward output,
+    statistics, and the backward with the mask and a second gradient branch (residual fan-in).  Tolerances: statistics
+    1e-5 relative (float32 accumulation over 802,816 rows vs float64), outputs one bf16 rounding of the float64 value
+    (the gradient sum of two branches is rounded from float32 once) on all but < 1e-5 of the elements (those whose
+    pre-activation lies within float32 rounding of the ReLU boundary may fall on either side), d(gamma)/d(beta) 2e-3 of
+    the vector's scale."""
+    from oracle import batchnorm as obn
+    m, c = 256 * 56 * 56, 256
+    cabi.tune_set("bn_vec_bf16", 8)
+    g = torch.Generator(device=DEV).manual_seed(3)
+    mk = lambda s, o: (torch.randn(m, c, generator=g, device=DEV) * s + o).to(torch.bfloat16)  # noqa: E731
+    x, z, dy, dy2 = mk(1.7, 0.4), mk(1.0, 0.0), mk(1.0, 0.0), mk(0.5, 0.0)
+    gamma = (torch.rand(c, generator=g, device=DEV) + 0.5)
+    beta = torch.randn(c, generator=g, device=DEV) * 0.3
+    v4 = lambda t: t.view(1, m, 1, c).permute(0, 3, 1, 2)  # noqa: E731
+    rm, rv = torch.zeros(c, device=DEV), torch.ones(c, device=DEV)
+    y, saved, mask = cabi.bn_fwd_train(v4(x), v4(z), gamma, beta, rm, rv, None, 1e-5, 0.1, cabi.ACT_ADD_RELU)
+    dx, dz, dg, db = cabi.bn_bwd(v4(dy), v4(x), mask, gamma, saved, cabi.ACT_ADD_RELU, dy2=v4(dy2))
+    torch.cuda.synchronize()
+    f32 = lambda t: t.float().cpu().numpy().reshape(m, c)  # noqa: E731
+    o = obn.bn_fwd_bwd_chunked_oracle(f32(x), gamma.cpu().numpy(), beta.cpu().numpy(), f32(dy), obn.ACT_ADD_RELU, f32(z),
+                                      f32(dy2))
+    sv = saved.cpu().numpy().astype(np.float64)
+    assert np.allclose(sv[0], o["mean"], rtol=1e-5, atol=1e-6) and np.allclose(sv[1], o["invstd"], rtol=1e-5)
+    assert np.allclose(rv.cpu().numpy(), 0.9 + 0.1 * o["var_unbiased"], rtol=1e-5)
+
+    def close_bf16(got, want, what):
+        got = got.permute(0, 2, 3, 1).float().cpu().numpy().reshape(m, c)
+        err = np.abs(got - want)
+        tol = np.abs(want) * 2.0 ** -8 + np.abs(want).max() * 2.0 ** -16 + 1e-6
+        bad = err > tol
+        # elements whose pre-activation sits within float32 rounding of zero may legitimately fall on the other side of
+        # the ReLU; they are counted, not tolerated silently
+        assert bad.mean() < 1e-5, (what, float(bad.mean()), float(err.max()))
+
+    close_bf16(y, o["y"], "y")
+    close_bf16(dz, o["dz"], "dz")
+    close_bf16(dx, o["dx"], "dx")
+    scale_g, scale_b = np.abs(o["dgamma"]).max(), np.abs(o["dbeta"]).max()
+    assert np.abs(dg.cpu().numpy() - o["dgamma"]).max() <= 2e-3 * scale_g     # (a boundary element moves a sum by ~1)
+    assert np.abs(db.cpu().numpy() - o["dbeta"]).max() <= 2e-3 * scale_b
+
+
 def test_bn_golden_case_from_torch():
     c = np.load(os.path.join(GOLD, "bn_case.npz"))
 
