@@ -130,6 +130,48 @@ def graph_level(rank, local, world):
     return out
 
 
+def timeout_level(rank, world, dev, n=1 << 16):
+    """A peer that never shows up: rank 0 launches the exchange of one bucket, the other ranks launch nothing.  Rank
+    0's kernel must give up after its ~20 s wait, latch the error word and leave EVERY arena untouched (its own and,
+    through the peer mappings, everybody else's); the iteration counter must not advance; later launches return at
+    once without touching anything either."""
+    import time
+
+    import torch.distributed._symmetric_memory as symm_mem
+
+    p0 = torch.randn(n, generator=torch.Generator().manual_seed(3))
+    grad = symm_mem.empty(n, dtype=torch.float32, device=dev).fill_(1.0)
+    param = symm_mem.empty(n, dtype=torch.float32, device=dev)
+    shadow = symm_mem.empty(n, dtype=torch.bfloat16, device=dev).zero_()
+    pad = symm_mem.empty(_cabi.peer_pad_words(), dtype=torch.int32, device=dev).zero_()
+    param.copy_(p0)
+    mom = torch.zeros(n, device=dev)
+    tabs = [_cabi.peer_table(symm_mem.rendezvous(t, dist.group.WORLD).buffer_ptrs) for t in (grad, param, shadow, pad)]
+    torch.cuda.synchronize()
+    dist.barrier()
+    t0 = time.time()
+    if rank == 0:
+        _cabi.peer_exchange_sgd(tabs[0], tabs[1], tabs[2], tabs[3], mom, rank, world, 0, 0, n, 0.1, 1e-4, 0.9, 1.0, True, 8)
+        _cabi.peer_wait(pad, world, 1, rank)
+        torch.cuda.synchronize()
+        waited = time.time() - t0
+        # latched: a second attempt returns immediately
+        t1 = time.time()
+        _cabi.peer_exchange_sgd(tabs[0], tabs[1], tabs[2], tabs[3], mom, rank, world, 0, 0, n, 0.1, 1e-4, 0.9, 1.0, False, 8)
+        _cabi.peer_wait(pad, world, 1, rank)
+        torch.cuda.synchronize()
+        second = time.time() - t1
+    else:
+        waited = second = 0.0
+    dist.barrier()      # (a host-side barrier over NCCL's own stream: the other ranks just wait here for rank 0)
+    torch.cuda.synchronize()
+    ok = torch.tensor([float(torch.equal(param.cpu(), p0) and float(mom.abs().sum()) == 0.0
+                             and float(shadow.float().abs().sum()) == 0.0)], device=dev)
+    dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+    return {"error_word_rank0": int(pad[0].item()) if rank == 0 else None, "step_counter": int(pad[1].item()),
+            "all_arenas_untouched_on_all_ranks": bool(ok.item() == 1.0), "waited_s": waited, "second_attempt_s": second}
+
+
 def timing(rank, world, dev, n=25557056):
     import torch.distributed._symmetric_memory as symm_mem
 
@@ -182,6 +224,8 @@ def main():
         out["graph"] = graph_level(rank, local, world)
     if os.environ.get("B200_PEER_TIMING", "1") == "1":
         out["timing"] = timing(rank, world, dev)
+    if os.environ.get("B200_PEER_TIMEOUT", "0") == "1":     # last: it leaves an error latched in its own pad only
+        out["timeout"] = timeout_level(rank, world, dev)
     if rank == 0:
         print(json.dumps(out))
     dist.destroy_process_group()

@@ -46,3 +46,19 @@ def test_two_gpu_peer_exchange_matches_closed_form_and_nccl_path():
     assert a["epoch"][0] == pytest.approx(g["nccl"]["epoch"][0], rel=2e-3) and a["epoch"][1:] == g["nccl"]["epoch"][1:]
     assert a["w"] == pytest.approx(g["nccl"]["w"], rel=1e-4) and a["rv"] == pytest.approx(g["nccl"]["rv"], rel=1e-3)
     assert g["segmented_refuses_peer"]
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs")
+def test_two_gpu_peer_exchange_gives_up_cleanly_when_a_peer_never_arrives():
+    """~20 s: rank 1 never launches its half of the exchange.  Rank 0 must time out, report it, and nobody's parameters,
+    shadow or momentum may have been written (no update from gradients that were never known to be final)."""
+    env = dict(os.environ, PYTHONPATH=ROOT, B200_PEER_TIMING="0", B200_PEER_MODEL="0", B200_PEER_GRAPH="0",
+               B200_PEER_TIMEOUT="1")
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr",
+           "127.0.0.1", "--master-port", "29594", os.path.join(ROOT, "tests", "peer_exchange_worker.py")]
+    r = subprocess.run(cmd, env=env, capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-4000:]
+    t = json.loads([l for l in r.stdout.splitlines() if l.startswith("{")][-1])["timeout"]
+    assert t["error_word_rank0"] == 1 and t["step_counter"] == 0
+    assert t["all_arenas_untouched_on_all_ranks"]
+    assert 5.0 < t["waited_s"] < 120.0 and t["second_attempt_s"] < 2.0
