@@ -588,6 +588,9 @@ def run_ours(a):
         e2e = {"value": a.batch * world * a.steps / float(dt.item()), "unit": "images/s",
                "h2d_bytes_per_step": tl.h2d_bytes, "d2h_bytes_per_step": 12}
       except Exception as e:  # noqa: BLE001  (keep the device-resident measurement if the end-to-end loop fails)
+        import traceback
+
+        traceback.print_exc()
         notes.append(f"end-to-end region failed: {type(e).__name__}: {str(e)[:200]}")
         e2e = None
     clocks = sampler.stop() if rank == 0 else None

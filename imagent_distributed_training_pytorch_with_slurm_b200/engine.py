@@ -146,9 +146,11 @@ class GraphedStep:
         self.seen, self.graph, self.x, self.t, self.out3 = 0, None, None, None, None
         inner = getattr(model, "module", model)
         self.arena = getattr(inner, "arena", None)
-        # a process that also runs NCCL (FlatDDP(exchange="peer") keeps it for metrics) must not let NCCL's watchdog
-        # thread invalidate the capture: confine capture errors to this thread
-        self.capture_error_mode = "thread_local" if getattr(model, "exchange", "nccl") == "peer" else "global"
+        # Other threads of the process keep working while this one captures: the loader's producer thread allocates
+        # pinned host memory (which, in "global" mode, invalidates the capture whenever the two coincide - it did, once
+        # the warm-up epoch was long enough for the producer to still be busy at the fourth iteration), NCCL's watchdog
+        # polls events.  None of that touches the capturing stream, so capture errors are confined to this thread.
+        self.capture_error_mode = "thread_local"
 
     def _eager(self, x, t):
         logits = self.model(x)

@@ -230,6 +230,8 @@ class _Block(nn.Module):
         fused = None
         if self.downsample is not None:
             dbn = self.downsample[1]
+            # (Running this branch on the side stream beside the main branch was tried: 19.13-19.15 ms per ResNet-50
+            # step with it against 19.15 without, same box - both branches are HBM-bound most of the time.)
             td = self.downsample[0].fwd(x)
             tape["td"] = td
             if _cabi.bn_dual_supported(t):
