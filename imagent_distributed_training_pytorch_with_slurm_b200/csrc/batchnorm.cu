@@ -157,7 +157,10 @@ PipeGeom make_geom_pipe(int64_t m, int c, int vec, int esize, int nt, bool mask,
     int st = (int)((budget > static_smem + kRingHeader ? budget - static_smem - kRingHeader : 0) / pipe_stage_bytes(nt, mask));
     if (st > kMaxStages) st = kMaxStages;
     if (st < 2) st = 2;
-    if (g_bn_pipe_stages > 0) st = g_bn_pipe_stages;
+    if (g_bn_pipe_stages > 0) {   // forced depth (tuning knob), but never more than fits beside the other resident CTAs
+        st = g_bn_pipe_stages;
+        while (st > 2 && static_smem + pipe_smem_bytes(nt, mask, st) > (size_t)220 * 1024 / per_sm) --st;
+    }
     pg.stages = st;
     pg.smem = pipe_smem_bytes(nt, mask, st);
     return pg;
