@@ -81,6 +81,44 @@ def _pil_decode(data, limit):
     return np.asarray(img)
 
 
+def _pil_open(data, limit):
+    """Header only: (lazy PIL image, integer shrink factor, height, width after the shrink)."""
+    import io
+
+    from PIL import Image
+
+    img = Image.open(io.BytesIO(data))
+    f = max(-(-img.height // limit[0]), -(-img.width // limit[1]), 1)
+    return img, f, -(-img.height // f), -(-img.width // f)
+
+
+def _pil_decode_into(img, f, dst):
+    """Decode (``convert("RGB")``, as pil_loader) straight into ``dst`` = uint8 [h, w, 3] view of the pinned slab."""
+    img = img.convert("RGB")
+    if f > 1:
+        img = img.reduce(f)
+    np.copyto(dst, np.asarray(img))
+
+
+class _PinnedSlabs:
+    """A few pinned host buffers reused round-robin for the decoded batches (allocating page-locked memory per batch
+    costs more than decoding it).  ``events[i]`` is recorded by the consumer after the host->device copy out of buffer i
+    was enqueued; the producer waits on it before writing into that buffer again."""
+
+    def __init__(self, count):
+        self.bufs, self.events, self.next = [None] * count, [None] * count, 0
+
+    def take(self, nbytes):
+        i = self.next
+        self.next = (i + 1) % len(self.bufs)
+        if self.events[i] is not None:
+            self.events[i].synchronize()
+            self.events[i] = None
+        if self.bufs[i] is None or self.bufs[i].numel() < nbytes:
+            self.bufs[i] = torch.empty(int(nbytes * 1.2) + 4096, dtype=torch.uint8).pin_memory()
+        return i, self.bufs[i]
+
+
 class ImageFolderLoader:
     """Iterable of ``(input, target)`` device tensors over an ``ImageFolderIndex`` in sampler order.
 
@@ -104,7 +142,7 @@ class ImageFolderLoader:
         self._draw = _Draw(self.gen)
         self.limit = (8 * self.out_h, 8 * self.out_w)
         self.h2d_bytes = 0           # bytes copied host -> device by the last batch
-        self._stream = None
+        self._slabs = _PinnedSlabs(self.prefetch + 3)
 
     def __len__(self):
         return -(-len(self.sampler) // self.batch_size)       # drop_last=False
@@ -153,8 +191,9 @@ class ImageFolderLoader:
         target = torch.tensor([self.index.samples[i][1] for i in ids], dtype=torch.int64)
         blobs = list(pool.map(self._read, paths))
         if self.decoder == "pil":
-            arrays = list(pool.map(lambda b: _pil_decode(b, self.limit), blobs))
-            sizes = [a.shape[:2] for a in arrays]
+            opened = list(pool.map(lambda b: _pil_open(b, self.limit), blobs))      # headers: sizes without decoding
+            sizes = [(h, w) for _, _, h, w in opened]
+            arrays = None
         else:
             probes = list(pool.map(self._probe, blobs))
             sizes = [(h, w) for h, w, _ in probes]
@@ -165,12 +204,17 @@ class ImageFolderLoader:
         item = {"table": table.pin_memory(), "boxes": boxes.pin_memory(), "flips": flips.pin_memory(),
                 "target": target.pin_memory(), "sizes": sizes, "offs": offs, "total": total}
         if self.decoder == "pil":
-            slab = torch.empty(total, dtype=torch.uint8).pin_memory()
+            # every worker decodes its image straight into its slot of a recycled pinned slab
+            slot, slab = self._slabs.take(total)
             sv = slab.numpy()
-            for a, o in zip(arrays, offs):
-                sv[o:o + a.size] = a.reshape(-1)
-            sv[total - _SLAB_TAIL:] = 0
-            item["slab"] = slab
+
+            def work(k):
+                img, f, h, w = opened[k]
+                _pil_decode_into(img, f, sv[offs[k]:offs[k] + h * w * 3].reshape(h, w, 3))
+
+            list(pool.map(work, range(len(opened))))
+            sv[total - _SLAB_TAIL:total] = 0
+            item["slab"], item["slot"] = slab[:total], slot
         else:
             item["blobs"], item["arrays"] = blobs, arrays
         return item
@@ -211,6 +255,9 @@ class ImageFolderLoader:
         table = item["table"].to(dev, non_blocking=True)
         if self.decoder == "pil":
             slab = item["slab"].to(dev, non_blocking=True)
+            ev = torch.cuda.Event()
+            ev.record()
+            self._slabs.events[item["slot"]] = ev          # the producer may refill this buffer once the copy is done
             self.h2d_bytes = total + len(sizes) * (32 + 16 + 1 + 8)
         else:
             planes = self._gpu_decode(item)
