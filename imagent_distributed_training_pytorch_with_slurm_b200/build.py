@@ -14,6 +14,9 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libb200_imagenet.so")
 SOURCES = ["api.cu", "sgd.cu", "ce_topk.cu", "batchnorm.cu", "input.cu", "maxpool.cu", "pack.cu", "peer_exchange.cu"]
+# the JPEG decode glue links libnvjpeg and therefore lives in a library of its own (loaded only for decoder="nvjpeg")
+JPEG_LIB = os.path.join(HERE, "libb200_jpeg.so")
+JPEG_SOURCES = ["jpeg.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17", "--shared",
               "-Xcompiler", "-fPIC", "-cudart", "shared"]
 
@@ -26,10 +29,11 @@ def _nvcc():
 
 
 def needs_build():
-    if not os.path.exists(LIB):
+    if not os.path.exists(LIB) or not os.path.exists(JPEG_LIB):
         return True
-    t = os.path.getmtime(LIB)
-    deps = [os.path.join(CSRC, f) for f in os.listdir(CSRC)] + [os.path.join(HERE, "..", "include", "b200_imagenet.h")]
+    t = min(os.path.getmtime(LIB), os.path.getmtime(JPEG_LIB))
+    deps = [os.path.join(CSRC, f) for f in os.listdir(CSRC)] + [os.path.join(HERE, "..", "include", h)
+                                                                 for h in ("b200_imagenet.h", "b200_jpeg.h")]
     return any(os.path.getmtime(d) > t for d in deps)
 
 
@@ -44,6 +48,11 @@ def build(force=False, verbose=False):
     os.replace(LIB + ".tmp", LIB)
     if verbose:
         sys.stderr.write(r.stderr)
+    cmd = [_nvcc()] + NVCC_FLAGS + [os.path.join(CSRC, s) for s in JPEG_SOURCES] + ["-lnvjpeg", "-o", JPEG_LIB + ".tmp"]
+    r = subprocess.run(cmd, capture_output=True, text=True)
+    if r.returncode != 0:
+        raise RuntimeError("nvcc failed:\n" + " ".join(cmd) + "\n" + r.stdout + r.stderr)
+    os.replace(JPEG_LIB + ".tmp", JPEG_LIB)
     return LIB
 
 

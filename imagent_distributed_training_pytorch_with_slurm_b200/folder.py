@@ -12,10 +12,14 @@ objects (imagenet.py:350-359).  What the reference does per image inside a worke
   * order      this package's ``DistributedSampler`` (bit-exact with torch's), ``drop_last=False`` batching like the
                reference's loaders - the last batch of an epoch is short;
   * decode     ``decoder="pil"``: Pillow in host threads, exactly the reference's pixels;
-               ``decoder="nvjpeg"``: nvJPEG on the GPU through ``torchvision.io.decode_jpeg(device="cuda")`` (a
-               LIBRARY call, like cuDNN for the convolutions), planar output re-packed by ``b200_interleave_planar_u8``;
-               files nvJPEG cannot take (CMYK, PNG-in-disguise, ...) fall back to Pillow one by one.  JPEG decoders
-               differ in IDCT rounding and chroma up-sampling, so this path is within a few grey levels of Pillow's,
+               ``decoder="nvjpeg"``: nvJPEG's batched API driven directly (``include/b200_jpeg.h``; a LIBRARY, like
+               cuDNN for the convolutions): the GPU's JPEG engines where a file allows it, otherwise the GPU-assisted
+               decoder with a pool of host threads for the Huffman stage, interleaved RGB written straight into the
+               slab, issued from the producer thread on a stream of its own;
+               ``decoder="torchvision"``: nvJPEG through ``torchvision.io.decode_jpeg(device="cuda")``, planar output
+               re-packed by ``b200_interleave_planar_u8`` (kept as a cross-check; torchvision serialises its decoder).
+               Files nvJPEG cannot take (CMYK, PNG-in-disguise, ...) are decoded by Pillow one by one.  JPEG decoders
+               differ in IDCT rounding and chroma up-sampling, so these paths are within a few grey levels of Pillow's,
                not bit-exact (measured in tests/test_gpu_folder.py);
   * transform  everything after the decode is the fused input kernel on the RAGGED batch
                (``b200_input_crop_resize_flip_norm_ragged``): images keep their own sizes in one byte slab, the crop box
@@ -130,8 +134,8 @@ class ImageFolderLoader:
     def __init__(self, index, sampler, batch_size, out_size=448, mean=IMAGENET_MEAN, std=IMAGENET_STD, random_crop=False,
                  dtype=torch.bfloat16, decoder="pil", workers=8, prefetch=2, seed=1234, rank=0, device=None,
                  layout=_cabi.LAYOUT_S2D_STEM):
-        if decoder not in ("pil", "nvjpeg"):
-            raise ValueError("decoder must be 'pil' or 'nvjpeg'")
+        if decoder not in ("pil", "nvjpeg", "torchvision"):
+            raise ValueError("decoder must be 'pil', 'nvjpeg' or 'torchvision'")
         self.index, self.sampler, self.batch_size = index, sampler, int(batch_size)
         self.out_h, self.out_w = (out_size, out_size) if isinstance(out_size, int) else out_size
         self.mean, self.std, self.random_crop, self.dtype = tuple(mean), tuple(std), random_crop, dtype
@@ -143,6 +147,7 @@ class ImageFolderLoader:
         self.limit = (8 * self.out_h, 8 * self.out_w)
         self.h2d_bytes = 0           # bytes copied host -> device by the last batch
         self._slabs = _PinnedSlabs(self.prefetch + 3)
+        self._jpeg = self._jpeg_stream = None        # decoder="nvjpeg": created by the producer thread on first use
 
     def __len__(self):
         return -(-len(self.sampler) // self.batch_size)       # drop_last=False
@@ -215,9 +220,49 @@ class ImageFolderLoader:
             list(pool.map(work, range(len(opened))))
             sv[total - _SLAB_TAIL:total] = 0
             item["slab"], item["slot"] = slab[:total], slot
+        elif self.decoder == "nvjpeg":
+            item["blobs"], item["arrays"] = blobs, arrays
+            self._decode_on_device(item)
         else:
             item["blobs"], item["arrays"] = blobs, arrays
         return item
+
+    def _decode_on_device(self, item):
+        """Producer thread: nvJPEG batched decode of the whole batch into a device slab, on this loader's own stream;
+        the consumer only waits for ``item["ready"]``.  Files the header probe kept for Pillow are copied in."""
+        from . import _jpeg
+
+        dev = self.device
+        with torch.cuda.device(dev):
+            if self._jpeg is None:
+                self._jpeg_stream = torch.cuda.Stream(device=dev)
+                self._jpeg = _jpeg.JpegDecoder(cpu_threads=self.workers, prefer_hardware=True)
+            sizes, offs, total, arrays = item["sizes"], item["offs"], item["total"], item["arrays"]
+            with torch.cuda.stream(self._jpeg_stream):
+                slab = torch.empty(total, dtype=torch.uint8, device=dev)
+                slab[total - _SLAB_TAIL:].zero_()
+                todo = [i for i, a in enumerate(arrays) if a is None]
+                for i, a in enumerate(arrays):
+                    if a is not None:
+                        slab[offs[i]:offs[i] + a.size].copy_(torch.from_numpy(np.ascontiguousarray(a)).view(-1))
+                if todo:
+                    sub = item["table"][todo].contiguous()
+                    try:
+                        self._jpeg.decode_batch([item["blobs"][i] for i in todo], slab, sub)
+                    except _jpeg.JpegError as e:
+                        if e.code not in (_jpeg.NOT_SUPPORTED, _jpeg.BAD_JPEG):
+                            raise
+                        for i in todo:      # find the file(s) nvJPEG refuses and give exactly those to Pillow
+                            try:
+                                self._jpeg.decode_batch([item["blobs"][i]], slab, item["table"][i:i + 1].contiguous())
+                            except _jpeg.JpegError:
+                                a = _pil_decode(item["blobs"][i], self.limit)
+                                slab[offs[i]:offs[i] + a.size].copy_(torch.from_numpy(np.ascontiguousarray(a)).view(-1))
+                ev = torch.cuda.Event()
+                ev.record()
+            item["slab_dev"], item["ready"] = slab, ev
+            item["hw_count"] = self._jpeg.last_hardware_count
+            self._jpeg_stream.synchronize()      # the byte strings and the staging arrays may go once the GPU has them
 
     # ---- device side of one batch (consumer thread) ---------------------------------------------------
     def _gpu_decode(self, item):
@@ -259,6 +304,12 @@ class ImageFolderLoader:
             ev.record()
             self._slabs.events[item["slot"]] = ev          # the producer may refill this buffer once the copy is done
             self.h2d_bytes = total + len(sizes) * (32 + 16 + 1 + 8)
+        elif self.decoder == "nvjpeg":
+            slab = item["slab_dev"]
+            torch.cuda.current_stream(dev).wait_event(item["ready"])
+            slab.record_stream(torch.cuda.current_stream(dev))
+            self.last_hw_count = item["hw_count"]
+            self.h2d_bytes = sum(len(b) for b in item["blobs"]) + len(sizes) * (32 + 16 + 1 + 8)
         else:
             planes = self._gpu_decode(item)
             slab = torch.empty(total, dtype=torch.uint8, device=dev)

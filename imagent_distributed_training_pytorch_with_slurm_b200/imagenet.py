@@ -197,8 +197,9 @@ def build_parser():
     parser.add_argument("--data", type=str, default=None, metavar="DIR",
                         help="dataset root holding train/<class>/*.JPEG and val/<class>/*.JPEG, i.e. what "
                              "datasets.ImageNet reads after extraction (default: the reference's ../data/imagenet)")
-    parser.add_argument("--decoder", type=str, default="pil", choices=["pil", "nvjpeg"],
-                        help="JPEG decoding: Pillow in host threads (the reference's pixels) or nvJPEG on the GPU")
+    parser.add_argument("--decoder", type=str, default="pil", choices=["pil", "nvjpeg", "torchvision"],
+                        help="JPEG decoding: Pillow in host threads (the reference's pixels), nvJPEG's batched API on the "
+                             "GPU (JPEG engines where the files allow), or nvJPEG through torchvision")
     parser.add_argument("--workers", type=int, default=10, help="host threads reading / decoding files (reference: 10 "
                                                                 "DataLoader workers)")
     parser.add_argument("--random-crop", action="store_true", default=False,

@@ -23,6 +23,21 @@ def test_library_exports_every_declared_symbol():
     assert set(names) == set(cabi.SIGNATURES), set(names) ^ set(cabi.SIGNATURES)
 
 
+def test_jpeg_library_exports_every_declared_symbol():
+    """include/b200_jpeg.h <-> libb200_jpeg.so <-> the ctypes table (loading it needs libnvjpeg, no GPU)."""
+    import imagent_distributed_training_pytorch_with_slurm_b200._jpeg as jpeg
+
+    src = open(os.path.join(ROOT, "include", "b200_jpeg.h")).read()
+    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+    names = sorted(set(re.findall(r"\b(b200_jpeg_[a-z0-9_]+)\s*\(", src)))
+    assert len(names) == 7 and set(names) == set(jpeg.SIGNATURES), set(names) ^ set(jpeg.SIGNATURES)
+    lib = ctypes.CDLL(jpeg.LIB_PATH)
+    for n in names:
+        assert hasattr(lib, n), n
+    assert jpeg.load().b200_jpeg_error_string(1004).decode().endswith("not supported")
+    assert jpeg.load().b200_jpeg_error_string(0) == b"success"
+
+
 def test_binding_loads_and_reports_version_and_sizes():
     lib = cabi.load()
     assert lib.b200_abi_version() == cabi.ABI_VERSION

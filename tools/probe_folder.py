@@ -34,7 +34,7 @@ nbytes = sum(os.path.getsize(os.path.join(dp, f)) for dp, _, fs in os.walk(root)
 print(json.dumps({"dataset": N, "jpeg_MB": round(nbytes / 1e6, 1), "made_in_s": round(time.time() - t0, 1),
                   "cores": len(os.sched_getaffinity(0))}), flush=True)
 idx = b200.ImageFolderIndex(root, "train")
-for decoder, workers in (("pil", 8), ("pil", len(os.sched_getaffinity(0))), ("nvjpeg", 4), ("nvjpeg", 8)):
+for decoder, workers in (("pil", 8), ("nvjpeg", 8), ("nvjpeg", 16), ("torchvision", 8)):
     for mode, out, crop in (("reference 448 whole image", 448, False), ("random crop 224", 224, True)):
         sampler = b200.DistributedSampler(idx, num_replicas=1, rank=0)
         loader = b200.ImageFolderLoader(idx, sampler, 256, out_size=out, random_crop=crop, decoder=decoder, workers=workers,
@@ -49,4 +49,5 @@ for decoder, workers in (("pil", 8), ("pil", len(os.sched_getaffinity(0))), ("nv
             torch.cuda.synchronize()
             dt = time.perf_counter() - t0
         print(json.dumps({"decoder": decoder, "workers": workers, "mode": mode, "images_per_s": round(n / dt),
-                          "h2d_MB_per_batch": round(loader.h2d_bytes / 1e6, 1)}), flush=True)
+                          "h2d_MB_per_batch": round(loader.h2d_bytes / 1e6, 1),
+                          "hardware_engine_images_in_last_batch": getattr(loader, "last_hw_count", None)}), flush=True)
