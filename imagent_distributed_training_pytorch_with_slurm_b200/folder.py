@@ -244,7 +244,7 @@ class ImageFolderLoader:
                 todo = [i for i, a in enumerate(arrays) if a is None]
                 for i, a in enumerate(arrays):
                     if a is not None:
-                        slab[offs[i]:offs[i] + a.size].copy_(torch.from_numpy(np.ascontiguousarray(a)).view(-1))
+                        slab[offs[i]:offs[i] + a.size].copy_(torch.from_numpy(np.array(a, copy=True)).view(-1))
                 if todo:
                     sub = item["table"][todo].contiguous()
                     try:
@@ -257,11 +257,12 @@ class ImageFolderLoader:
                                 self._jpeg.decode_batch([item["blobs"][i]], slab, item["table"][i:i + 1].contiguous())
                             except _jpeg.JpegError:
                                 a = _pil_decode(item["blobs"][i], self.limit)
-                                slab[offs[i]:offs[i] + a.size].copy_(torch.from_numpy(np.ascontiguousarray(a)).view(-1))
+                                slab[offs[i]:offs[i] + a.size].copy_(torch.from_numpy(np.array(a, copy=True)).view(-1))
                 ev = torch.cuda.Event()
                 ev.record()
             item["slab_dev"], item["ready"] = slab, ev
             item["hw_count"] = self._jpeg.last_hardware_count
+            self.jpeg_has_hardware = self._jpeg.has_hardware
             self._jpeg_stream.synchronize()      # the byte strings and the staging arrays may go once the GPU has them
 
     # ---- device side of one batch (consumer thread) ---------------------------------------------------

@@ -50,4 +50,5 @@ for decoder, workers in (("pil", 8), ("nvjpeg", 8), ("nvjpeg", 16), ("torchvisio
             dt = time.perf_counter() - t0
         print(json.dumps({"decoder": decoder, "workers": workers, "mode": mode, "images_per_s": round(n / dt),
                           "h2d_MB_per_batch": round(loader.h2d_bytes / 1e6, 1),
-                          "hardware_engine_images_in_last_batch": getattr(loader, "last_hw_count", None)}), flush=True)
+                          "hardware_engine_images_in_last_batch": getattr(loader, "last_hw_count", None),
+                          "hardware_backend_created": getattr(loader, "jpeg_has_hardware", None)}), flush=True)
