@@ -147,7 +147,8 @@ class ImageFolderLoader:
         self.limit = (8 * self.out_h, 8 * self.out_w)
         self.h2d_bytes = 0           # bytes copied host -> device by the last batch
         self._slabs = _PinnedSlabs(self.prefetch + 3)
-        self._jpeg = self._jpeg_stream = None        # decoder="nvjpeg": created by the producer thread on first use
+        self._jpeg_tls = threading.local()           # decoder="nvjpeg": one nvJPEG decoder + stream per decode thread
+        self.decode_threads = 2                      # batches being decoded on the device at the same time
 
     def __len__(self):
         return -(-len(self.sampler) // self.batch_size)       # drop_last=False
@@ -221,24 +222,25 @@ class ImageFolderLoader:
             sv[total - _SLAB_TAIL:total] = 0
             item["slab"], item["slot"] = slab[:total], slot
         elif self.decoder == "nvjpeg":
-            item["blobs"], item["arrays"] = blobs, arrays
-            self._decode_on_device(item)
+            item["blobs"], item["arrays"] = blobs, arrays     # decoded by a decode thread (see __iter__)
         else:
             item["blobs"], item["arrays"] = blobs, arrays
         return item
 
     def _decode_on_device(self, item):
-        """Producer thread: nvJPEG batched decode of the whole batch into a device slab, on this loader's own stream;
-        the consumer only waits for ``item["ready"]``.  Files the header probe kept for Pillow are copied in."""
+        """Decode thread: nvJPEG batched decode of the whole batch into a device slab, on that thread's own decoder
+        object and stream; the consumer only waits for ``item["ready"]``.  Files the header probe kept for Pillow are
+        copied in."""
         from . import _jpeg
 
-        dev = self.device
+        dev, tls = self.device, self._jpeg_tls
         with torch.cuda.device(dev):
-            if self._jpeg is None:
-                self._jpeg_stream = torch.cuda.Stream(device=dev)
-                self._jpeg = _jpeg.JpegDecoder(cpu_threads=self.workers, prefer_hardware=True)
+            if getattr(tls, "jpeg", None) is None:
+                tls.stream = torch.cuda.Stream(device=dev)
+                tls.jpeg = _jpeg.JpegDecoder(cpu_threads=max(1, self.workers // self.decode_threads), prefer_hardware=True)
+            jpeg, stream = tls.jpeg, tls.stream
             sizes, offs, total, arrays = item["sizes"], item["offs"], item["total"], item["arrays"]
-            with torch.cuda.stream(self._jpeg_stream):
+            with torch.cuda.stream(stream):
                 slab = torch.empty(total, dtype=torch.uint8, device=dev)
                 slab[total - _SLAB_TAIL:].zero_()
                 todo = [i for i, a in enumerate(arrays) if a is None]
@@ -248,22 +250,23 @@ class ImageFolderLoader:
                 if todo:
                     sub = item["table"][todo].contiguous()
                     try:
-                        self._jpeg.decode_batch([item["blobs"][i] for i in todo], slab, sub)
+                        jpeg.decode_batch([item["blobs"][i] for i in todo], slab, sub)
                     except _jpeg.JpegError as e:
                         if e.code not in (_jpeg.NOT_SUPPORTED, _jpeg.BAD_JPEG):
                             raise
                         for i in todo:      # find the file(s) nvJPEG refuses and give exactly those to Pillow
                             try:
-                                self._jpeg.decode_batch([item["blobs"][i]], slab, item["table"][i:i + 1].contiguous())
+                                jpeg.decode_batch([item["blobs"][i]], slab, item["table"][i:i + 1].contiguous())
                             except _jpeg.JpegError:
                                 a = _pil_decode(item["blobs"][i], self.limit)
                                 slab[offs[i]:offs[i] + a.size].copy_(torch.from_numpy(np.array(a, copy=True)).view(-1))
                 ev = torch.cuda.Event()
                 ev.record()
             item["slab_dev"], item["ready"] = slab, ev
-            item["hw_count"] = self._jpeg.last_hardware_count
-            self.jpeg_has_hardware = self._jpeg.has_hardware
-            self._jpeg_stream.synchronize()      # the byte strings and the staging arrays may go once the GPU has them
+            item["hw_count"] = jpeg.last_hardware_count
+            self.jpeg_has_hardware = jpeg.has_hardware
+            stream.synchronize()      # the byte strings and the staging arrays may go once the GPU has them
+        return item
 
     # ---- device side of one batch (consumer thread) ---------------------------------------------------
     def _gpu_decode(self, item):
@@ -334,6 +337,9 @@ class ImageFolderLoader:
         batches = [ids[i:i + self.batch_size] for i in range(0, len(ids), self.batch_size)]
         q = queue.Queue(maxsize=self.prefetch)
         pool = ThreadPoolExecutor(self.workers)
+        # decoder="nvjpeg": the producer prepares batches in order (file reads, header probe, crop draws) and hands each
+        # to one of `decode_threads` decode threads; the queue carries the futures, so batches still arrive in order
+        dec = ThreadPoolExecutor(self.decode_threads) if self.decoder == "nvjpeg" else None
         stop = threading.Event()
 
         def put(item):
@@ -348,7 +354,10 @@ class ImageFolderLoader:
         def produce():
             try:
                 for b in batches:
-                    if not put(self._host_batch(pool, b)):
+                    item = self._host_batch(pool, b)
+                    if dec is not None:
+                        item = dec.submit(self._decode_on_device, item)
+                    if not put(item):
                         return
             except BaseException as e:  # noqa: BLE001  (surface it in the consumer)
                 put(e)
@@ -359,7 +368,11 @@ class ImageFolderLoader:
                 item = q.get()
                 if isinstance(item, BaseException):
                     raise item
+                if dec is not None:
+                    item = item.result()
                 yield self._stage(item)
         finally:
             stop.set()
             pool.shutdown(wait=False, cancel_futures=True)
+            if dec is not None:
+                dec.shutdown(wait=False, cancel_futures=True)
