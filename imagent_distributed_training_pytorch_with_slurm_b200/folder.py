@@ -236,7 +236,9 @@ class ImageFolderLoader:
         dev, tls = self.device, self._jpeg_tls
         with torch.cuda.device(dev):
             if getattr(tls, "jpeg", None) is None:
-                tls.stream = torch.cuda.Stream(device=dev)
+                # high priority: beside a training step that keeps every SM busy, the decode kernels of the NEXT batches
+                # must not queue behind a whole iteration's worth of already-enqueued work
+                tls.stream = torch.cuda.Stream(device=dev, priority=-1)
                 tls.jpeg = _jpeg.JpegDecoder(cpu_threads=max(1, self.workers // self.decode_threads), prefer_hardware=True)
             jpeg, stream = tls.jpeg, tls.stream
             sizes, offs, total, arrays = item["sizes"], item["offs"], item["total"], item["arrays"]
