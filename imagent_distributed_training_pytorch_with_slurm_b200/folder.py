@@ -149,6 +149,23 @@ class ImageFolderLoader:
         self._slabs = _PinnedSlabs(self.prefetch + 3)
         self._jpeg_tls = threading.local()           # decoder="nvjpeg": one nvJPEG decoder + stream per decode thread
         self.decode_threads = 2                      # batches being decoded on the device at the same time
+        self._pool = self._dec = None                # thread pools, created on first use and kept across epochs (the
+        #                                              decode threads own nvJPEG decoder objects: creating those per epoch
+        #                                              would cost device allocations every time)
+
+    def _pools(self):
+        if self._pool is None:
+            self._pool = ThreadPoolExecutor(self.workers, thread_name_prefix="b200-io")
+            if self.decoder == "nvjpeg":
+                self._dec = ThreadPoolExecutor(self.decode_threads, thread_name_prefix="b200-jpeg")
+        return self._pool, self._dec
+
+    def close(self):
+        """Stop the worker threads (the nvJPEG decoder objects go with their threads)."""
+        for ex in (self._pool, self._dec):
+            if ex is not None:
+                ex.shutdown(wait=False, cancel_futures=True)
+        self._pool = self._dec = None
 
     def __len__(self):
         return -(-len(self.sampler) // self.batch_size)       # drop_last=False
@@ -338,10 +355,9 @@ class ImageFolderLoader:
         ids = self.sampler.indices().tolist()
         batches = [ids[i:i + self.batch_size] for i in range(0, len(ids), self.batch_size)]
         q = queue.Queue(maxsize=self.prefetch)
-        pool = ThreadPoolExecutor(self.workers)
         # decoder="nvjpeg": the producer prepares batches in order (file reads, header probe, crop draws) and hands each
         # to one of `decode_threads` decode threads; the queue carries the futures, so batches still arrive in order
-        dec = ThreadPoolExecutor(self.decode_threads) if self.decoder == "nvjpeg" else None
+        pool, dec = self._pools()
         stop = threading.Event()
 
         def put(item):
@@ -374,7 +390,11 @@ class ImageFolderLoader:
                     item = item.result()
                 yield self._stage(item)
         finally:
-            stop.set()
-            pool.shutdown(wait=False, cancel_futures=True)
-            if dec is not None:
-                dec.shutdown(wait=False, cancel_futures=True)
+            stop.set()                     # an early exit: the producer stops, decodes not yet started are dropped
+            while True:
+                try:
+                    item = q.get_nowait()
+                except queue.Empty:
+                    break
+                if dec is not None and hasattr(item, "cancel"):
+                    item.cancel()
